@@ -1,0 +1,12 @@
+"""dynosam_b200: B200-native backend Levenberg-Marquardt solve for DynoSAM graphs.
+
+The product is libdynosam_b200.so (hand-written sm_100a CUDA behind the C ABI of
+include/dynosam_b200.h); this package is the thin host mirror of the reference's
+backend interface for that path. There is no CPU fallback.
+"""
+from .api import (  # noqa: F401
+    BackendParams, CameraPoseSymbol, DynamicLandmarkSymbol, DynoError, GpuLevenbergMarquardt, Graph, LmParams,
+    ObjectMotionSymbol, ObjectPoseSymbol, Scene, StaticLandmarkSymbol, SyntheticConfig, ValuesKeyDoesNotExist,
+    cantor_depair, cantor_pair, default_backend_params, default_lm_params, default_synthetic_config, key_decode,
+    sliding_window_schedule,
+)
