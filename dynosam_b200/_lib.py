@@ -17,7 +17,7 @@ class LmParams(C.Structure):
         ("lambda_initial", C.c_double), ("lambda_factor", C.c_double), ("lambda_upper_bound", C.c_double),
         ("lambda_lower_bound", C.c_double), ("min_model_fidelity", C.c_double), ("max_iterations", C.c_int32),
         ("relative_error_tol", C.c_double), ("absolute_error_tol", C.c_double), ("error_tol", C.c_double),
-        ("pcg_rel_tol", C.c_double), ("pcg_max_iterations", C.c_int32), ("dense_threshold", C.c_int32),
+        ("pcg_rel_tol", C.c_double), ("pcg_max_iterations", C.c_int32), ("linear_solver", C.c_int32),
         ("device", C.c_int32), ("verbose", C.c_int32),
     ]
 

@@ -86,6 +86,7 @@ struct DeviceWork {
   double* Dinv = nullptr;      // 6 per slot
   double* Sig = nullptr;       // 6 per slot: diagonal block of M^-1
   double* SigOff = nullptr;    // 9 per slot: block (slot-32, slot) of M^-1
+  double* G = nullptr;         // 9 per slot: Dinv_{slot-32} B_slot (chain back-substitution gain)
   double* Pinv = nullptr;      // 36 per pose: inverse of the reduced diagonal block
   // vectors
   double* u = nullptr;         // 4 per slot
@@ -97,12 +98,27 @@ struct DeviceWork {
   int* flags = nullptr;        // [0] not-PD flag
 };
 
+// Reduced (Schur) system on the pose variables in time order, lower band storage:
+// element (r, c), r - bw <= c <= r, lives at S[r * ld + (c - r + bw)], ld = bw + 1.
+// Rows n..n_pad-1 are identity padding so that panels of kBandNB columns are whole.
+constexpr int kBandNB = 32;     // Cholesky panel width (scalars)
+constexpr int kBandTile = 64;   // trailing-update tile edge
+struct BandSystem {
+  int n = 0, n_pad = 0, bw = 0, ld = 0, window = 0;  // window = rows below a panel that it can touch (multiple of kBandTile)
+  const int* pose_pos = nullptr;   // [n_pose] position of pose a in time order
+  const int* pos_pose = nullptr;   // [n_pose] inverse
+  const int* row_first = nullptr;  // [n_pose] first block column (position) of the envelope of row p
+  double* S = nullptr;             // n_pad * ld
+  double* y = nullptr;             // n_pad, right-hand side / solution in time order
+};
+
 enum Scal : int {
   kErr = 0,        // nonlinear error of the evaluated state
   kLinOld = 1,     // 0.5 sum |b|^2
   kLinNew = 2,     // 0.5 sum |A d - b|^2
   kRz = 3, kRzNew = 4, kPAp = 5, kRhsNorm2 = 6, kRNorm2 = 7,
   kAlpha = 8, kBeta = 9, kDone = 10, kIters = 11, kBreakdown = 12,
+  kResNorm2 = 13,  // |rhs - S x|^2 of the direct (band) solve
   kNumScal = 16
 };
 

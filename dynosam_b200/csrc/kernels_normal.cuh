@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(256) k_build_poses(DeviceGraph g, const double
 
 // One lane per chain, one warp per slice of 32 chains.
 __global__ void __launch_bounds__(128) k_chain_factor(DeviceGraph g, double lambda, const double* __restrict__ V, const double* __restrict__ B,
-                                                      double* __restrict__ Dinv, double* __restrict__ Sig, double* __restrict__ SigOff, int* __restrict__ flags) {
+                                                      double* __restrict__ Dinv, double* __restrict__ Sig, double* __restrict__ SigOff, double* __restrict__ Gout, int* __restrict__ flags) {
   const int slice = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (slice >= g.n_slices) return;
@@ -132,6 +132,7 @@ __global__ void __launch_bounds__(128) k_chain_factor(DeviceGraph g, double lamb
     if (k < len - 1) {
       M3 Bn; for (int i = 0; i < 9; ++i) Bn.a[i] = B[9 * (size_t)(s + 32) + i];
       const M3 G = m3_mul(s3_full(Di), Bn);
+      for (int i = 0; i < 9; ++i) Gout[9 * (size_t)(s + 32) + i] = G.a[i];
       const M3 GS = m3_mul(G, s3_full(Snext));
       for (int i = 0; i < 9; ++i) SigOff[9 * (size_t)(s + 32) + i] = -GS.a[i];
       const M3 GSGt = m3_mul(GS, m3_t(G));
