@@ -396,6 +396,17 @@ __global__ void __launch_bounds__(1024) k_band_solve(BandSystem bs, int n_pose, 
   }
 }
 
+// FP64 FMA peak probe: 8 independent register chains per thread, 4096 FMAs each
+__global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters) {
+  double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double m = 1.0000001, c = 1e-9;
+  for (int i = 0; i < iters; ++i) {
+    a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+    a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
 __global__ void k_band_pad_identity(BandSystem bs) {
   for (int i = bs.n + threadIdx.x; i < bs.n_pad; i += blockDim.x) bs.S[(size_t)i * bs.ld + bs.bw] = 1.0;
 }
