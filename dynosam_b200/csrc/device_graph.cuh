@@ -101,8 +101,9 @@ struct DeviceWork {
 // Reduced (Schur) system on the pose variables in time order, lower band storage:
 // element (r, c), r - bw <= c <= r, lives at S[r * ld + (c - r + bw)], ld = bw + 1.
 // Rows n..n_pad-1 are identity padding so that panels of kBandNB columns are whole.
-constexpr int kBandNB = 32;     // Cholesky panel width (scalars)
+constexpr int kBandNB = 64;     // Cholesky panel width (scalars)
 constexpr int kBandTile = 64;   // trailing-update tile edge
+constexpr int kSolveNB = 32;    // block size of the triangular solves
 struct BandSystem {
   int n = 0, n_pad = 0, bw = 0, ld = 0, window = 0;  // window = rows below a panel that it can touch (multiple of kBandTile)
   const int* pose_pos = nullptr;   // [n_pose] position of pose a in time order
@@ -110,6 +111,8 @@ struct BandSystem {
   const int* row_first = nullptr;  // [n_pose] first block column (position) of the envelope of row p
   double* S = nullptr;             // n_pad * ld
   double* y = nullptr;             // n_pad, right-hand side / solution in time order
+  double* z = nullptr;             // n_pad, L^-1 rhs carried along by the factorisation
+  const int* first64 = nullptr;    // [n_pad / 64] smallest first envelope column over each group of 64 rows
 };
 
 enum Scal : int {

@@ -202,129 +202,12 @@ __global__ void __launch_bounds__(256) k_schur_assemble(DeviceGraph g, BandSyste
   }
 }
 
-// ---------------------------------------------------------------------------
-// Band Cholesky, right-looking, panels of kBandNB columns, one cooperative grid.
-//   phase 1 (per panel): every CTA factors the kBandNB x kBandNB diagonal block in shared memory
-//                        (redundantly: it is tiny and saves a grid barrier), then the rows below
-//                        the panel are solved against it, one warp per row, spread over the grid.
-//   phase 2            : trailing update of the (window x window) lower triangle below the panel,
-//                        64 x 64 tiles spread over the grid, 4 x 4 register tiles per thread.
-// flags |= 4 when a pivot is not positive (the analogue of IndeterminantLinearSystemException).
-// ---------------------------------------------------------------------------
-constexpr int kCholThreads = 256;
-
-__global__ void __launch_bounds__(kCholThreads) k_band_cholesky(BandSystem bs, int* __restrict__ flags) {
-  cg::grid_group grid = cg::this_grid();
-  constexpr int NB = kBandNB, TT = kBandTile;
-  __shared__ double D[NB][NB + 1];
-  __shared__ double LrT[NB][TT];   // [k][row]
-  __shared__ double LcT[NB][TT];   // [k][col]
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int warps_per_cta = kCholThreads / 32;
-  const int gwarp = blockIdx.x * warps_per_cta + wid, nwarp = gridDim.x * warps_per_cta;
-  const size_t ld = bs.ld;
-  const int bw = bs.bw;
-  double* __restrict__ S = bs.S;
-  for (int j0 = 0; j0 < bs.n_pad; j0 += NB) {
-    // ---- phase 1a: diagonal block ----
-    for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
-      const int r = idx / NB, c = idx - NB * r;
-      D[r][c] = (c <= r) ? S[(size_t)(j0 + r) * ld + (c - r + bw)] : 0.0;
-    }
-    __syncthreads();
-    for (int k = 0; k < NB; ++k) {
-      if (tid == 0) {
-        double d = D[k][k];
-        if (!(d > 0.0)) { if (blockIdx.x == 0) atomicOr(flags, 4); d = 1.0; }
-        D[k][k] = sqrt(d);
-      }
-      __syncthreads();
-      if (tid > k && tid < NB) D[tid][k] /= D[k][k];
-      __syncthreads();
-      for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
-        const int r = idx / NB, c = idx - NB * r;
-        if (c > k && c <= r) D[r][c] -= D[r][k] * D[c][k];
-      }
-      __syncthreads();
-    }
-    // ---- phase 1b: rows below the panel: x L_jj^T = a, lane k holds element k ----
-    const int i_begin = j0 + NB;
-    const int i_end = min(bs.n_pad, i_begin + bs.window);
-    for (int i = i_begin + gwarp; i < i_end; i += nwarp) {
-      double* rowp = S + (size_t)i * ld + (j0 - i + bw);
-      double v = rowp[lane];
-      for (int m = 0; m < NB; ++m) {
-        const double xm = __shfl_sync(0xffffffffu, v, m) / D[m][m];
-        if (lane == m) v = xm;
-        else if (lane > m) v -= xm * D[lane][m];
-      }
-      rowp[lane] = v;
-    }
-    grid.sync();
-    // the factored diagonal block goes back only now: before the barrier other CTAs may still be reading the unfactored one
-    if (blockIdx.x == 0)
-      for (int idx = tid; idx < NB * NB; idx += kCholThreads) {
-        const int r = idx / NB, c = idx - NB * r;
-        if (c <= r) S[(size_t)(j0 + r) * ld + (c - r + bw)] = D[r][c];
-      }
-    // ---- phase 2: trailing update ----
-    const int nt = (i_end - i_begin + TT - 1) / TT;
-    const int ntile = nt * (nt + 1) / 2;
-    for (int id = blockIdx.x; id < ntile; id += gridDim.x) {
-      int ti = (int)((sqrt(8.0 * id + 1.0) - 1.0) * 0.5);
-      while ((ti + 1) * (ti + 2) / 2 <= id) ++ti;
-      while (ti * (ti + 1) / 2 > id) --ti;
-      const int tj = id - ti * (ti + 1) / 2;
-      const int r0 = i_begin + ti * TT, c0 = i_begin + tj * TT;
-      __syncthreads();
-      {
-        const int rr = tid & (TT - 1), kq = tid >> 6;  // 64 rows x 4 k-chunks of 8
-        const int ir = r0 + rr, ic = c0 + rr;
-#pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          const int k = kq * 8 + kk;
-          LrT[k][rr] = (ir < i_end) ? S[(size_t)ir * ld + (j0 + k - ir + bw)] : 0.0;
-          LcT[k][rr] = (ic < i_end) ? S[(size_t)ic * ld + (j0 + k - ic + bw)] : 0.0;
-        }
-      }
-      __syncthreads();
-      const int ty = tid >> 4, tx = tid & 15;
-      double c[4][4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) c[i][j] = 0.0;
-#pragma unroll 8
-      for (int k = 0; k < NB; ++k) {
-        double a[4], b[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) a[i] = LrT[k][ty * 4 + i];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) b[j] = LcT[k][tx * 4 + j];
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) c[i][j] += a[i] * b[j];
-      }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int ir = r0 + ty * 4 + i;
-        if (ir >= i_end) continue;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int ic = c0 + tx * 4 + j;
-          if (ic <= ir) S[(size_t)ir * ld + (ic - ir + bw)] -= c[i][j];
-        }
-      }
-    }
-    grid.sync();
-  }
-}
-
 // x = L^-T L^-1 b with the band factor; b and x are in natural pose order (6 per pose), bs.y is scratch.
-// add_to_x: x += solution (iterative refinement) instead of x = solution. Single CTA of 1024 threads.
-__global__ void __launch_bounds__(1024) k_band_solve(BandSystem bs, int n_pose, const double* __restrict__ b, double* __restrict__ x, int add_to_x) {
-  constexpr int NB = kBandNB;
+// add_to_x: x += solution (iterative refinement) instead of x = solution. use_z: the forward substitution
+// was already carried along by the factorisation (bs.z = L^-1 rhs), only the backward half runs.
+// Single CTA of 1024 threads.
+__global__ void __launch_bounds__(1024) k_band_solve(BandSystem bs, int n_pose, const double* __restrict__ b, double* __restrict__ x, int add_to_x, int use_z) {
+  constexpr int NB = kSolveNB;
   __shared__ double D[NB][NB + 1];
   __shared__ double part[32][NB + 1];
   __shared__ double rs[NB];
@@ -335,12 +218,13 @@ __global__ void __launch_bounds__(1024) k_band_solve(BandSystem bs, int n_pose, 
   double* __restrict__ y = bs.y;
   for (int i = tid; i < bs.n_pad; i += blockDim.x) {
     double v = 0.0;
-    if (i < bs.n) { const int p = i / 6, c = i - 6 * p; v = b[6 * (size_t)bs.pos_pose[p] + c]; }
+    if (use_z) v = bs.z[i];
+    else if (i < bs.n) { const int p = i / 6, c = i - 6 * p; v = b[6 * (size_t)bs.pos_pose[p] + c]; }
     y[i] = v;
   }
   __syncthreads();
   // ---- forward: y_panel = L_jj^-1 (b_panel - L[panel, window before] y) ----
-  for (int j0 = 0; j0 < bs.n_pad; j0 += NB) {
+  for (int j0 = 0; j0 < (use_z ? 0 : bs.n_pad); j0 += NB) {
     for (int idx = tid; idx < NB * NB; idx += blockDim.x) {
       const int r = idx / NB, c = idx - NB * r;
       D[r][c] = (c <= r) ? S[(size_t)(j0 + r) * ld + (c - r + bw)] : 0.0;
