@@ -8,7 +8,7 @@ CFG = {"cfg2": dict(), "cfg3": dict(n_frames=1000, n_objects=20, static_per_fram
 for name in which:
     kw = CFG[name]
     t = time.time(); s = d.Scene.synthetic(**kw); g = s.full_batch_graph(); print(name, "build", time.time() - t, g.n_pose, g.n_point, g.n_p2p, g.n_ternary, g.n_between, flush=True)
-    p = d.default_lm_params(); p.max_iterations = 5; p.relative_error_tol = 0; p.absolute_error_tol = 0; p.verbose = 2
+    p = d.default_lm_params(); p.max_iterations = 5; p.relative_error_tol = 0; p.absolute_error_tol = 0; p.verbose = int(__import__("os").environ.get("DV", "2"))
     t = time.time(); lm = d.GpuLevenbergMarquardt(g, p); print("load", time.time() - t, flush=True)
     t = time.time(); lm.optimize(); print("opt wall", time.time() - t); print(lm.timing(), lm.error_trace, flush=True)
     if name == "mid":
