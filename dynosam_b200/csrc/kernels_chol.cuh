@@ -269,6 +269,81 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
   if (prof && blockIdx.x == 0) for (int k = 1; k < 4; ++k) bs.prof[8 + k] = sub_t[k];
 }
 
+// Backward substitution x = L^-T z after k_band_cholesky (which left z = L^-1 rhs and the inverses of the
+// diagonal blocks). Small cooperative grid, one barrier per 64-column panel, right-looking: every CTA forms
+// x_J = Linv_J^T z_J redundantly (64 x 64, read coalesced from L2), then the grid subtracts L[J rows, c] x_J from
+// the z entries of the window columns left of the panel, one column per thread (row-panel reads are contiguous).
+// x is written in natural pose order. z is consumed.
+constexpr int kBackThreads = 256;
+__global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, double* __restrict__ x) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double part[4][64];
+  __shared__ double xs[64];
+  const int tid = threadIdx.x;
+  const size_t ld = bs.ld;
+  const int bw = bs.bw;
+  const double* __restrict__ S = bs.S;
+  double* __restrict__ z = bs.z;
+  const int gtid = blockIdx.x * kBackThreads + tid, gsize = gridDim.x * kBackThreads;   // gsize >= window + 64
+  // a thread owns the columns congruent to gtid modulo gsize: at most one of them lies in the window of a panel, and
+  // it stays the same from panel to panel until the panels reach it, so its z entry lives in a register meanwhile
+  auto column_of = [&](int j0) {
+    int d = (j0 - 1 - gtid) % gsize;
+    if (d < 0) d += gsize;
+    const int c = j0 - 1 - d;
+    return (c >= 0 && c >= j0 - bs.window) ? c : -1;
+  };
+  const int k = tid & 63, pt = tid >> 6;
+  double lc[64], li[16];
+  auto prefetch = [&](int j0, int c) {
+    const double* Li = bs.Linv + (size_t)(j0 >> 6) * 4096;
+#pragma unroll
+    for (int mm = 0; mm < 16; ++mm) li[mm] = Li[(pt * 16 + mm) * 64 + k];   // Linv is zero above the diagonal
+    if (c >= 0) {
+      const double* col = S + (size_t)j0 * ld + (c - j0 + bw);   // element (j0 + rr, c) at col[rr * (ld - 1)]
+#pragma unroll
+      for (int rr = 0; rr < 64; ++rr) lc[rr] = (j0 + rr - c <= bw) ? col[(size_t)rr * (ld - 1)] : 0.0;
+    }
+  };
+  int j0 = bs.n_pad - 64;
+  int c = column_of(j0);
+  double zreg = c >= 0 ? z[c] : 0.0;
+  prefetch(j0, c);
+  for (; j0 >= 0; j0 -= 64) {
+    {  // x_k = sum_{m >= k} Linv[m][k] z_m
+      double s = 0.0;
+#pragma unroll
+      for (int mm = 0; mm < 16; ++mm) s = fma(li[mm], z[j0 + pt * 16 + mm], s);
+      part[pt][k] = s;
+    }
+    __syncthreads();
+    if (tid < 64) {
+      const double v = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
+      xs[tid] = v;
+      const int i = j0 + tid;
+      if (blockIdx.x == 0 && i < bs.n) { const int p = i / 6, cc = i - 6 * p; x[6 * (size_t)bs.pos_pose[p] + cc] = v; }
+    }
+    __syncthreads();
+    if (c >= 0) {
+      double s = 0.0;
+#pragma unroll
+      for (int rr = 0; rr < 64; ++rr) s = fma(lc[rr], xs[rr], s);
+      zreg -= s;
+    }
+    const int j1 = j0 - 64;
+    if (j1 >= 0) {
+      const int c1 = column_of(j1);
+      if (c1 != c) {
+        if (c >= 0) z[c] = zreg;              // c joins the next panel: publish before the barrier
+        zreg = c1 >= 0 ? z[c1] : 0.0;          // untouched so far
+        c = c1;
+      }
+      prefetch(j1, c);                          // in flight across the barrier
+    }
+    grid.sync();
+  }
+}
+
 // y[time order] = b[natural pose order]; zero on the padding
 __global__ void __launch_bounds__(256) k_band_load_rhs(BandSystem bs, const double* __restrict__ b) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

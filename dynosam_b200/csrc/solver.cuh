@@ -235,7 +235,7 @@ class LmSolver {
   DevBuf<double> d_S_, d_y_, d_zb_, d_Linv_, d_G_, d_res_;
   DevBuf<long long> d_prof_;
   bool band_ok_ = false, band_dirty_ = true, dpt_valid_ = false;
-  int chol_grid_ = 0, assemble_smem_ = 0;
+  int chol_grid_ = 0, back_grid_ = 0, assemble_smem_ = 0;
   std::string band_why_not_;
 };
 
