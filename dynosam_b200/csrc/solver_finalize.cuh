@@ -98,7 +98,29 @@ inline void LmSolver::finalize() {
   };
   std::vector<int> pp_ptr, pp_idx, pt_ptr, pt_idx, pb_ptr, pb_idx, pr_ptr, pr_idx;
   build_csr(n_entries, [&](int e) { return p2p_pose[e]; }, [&](int e) { return e; }, pp_ptr, pp_idx);
-  build_csr(n_slots, [&](int s) { return ter_motion[s]; }, [&](int s) { return s; }, pt_ptr, pt_idx);
+  {
+    // within a pose, keep the PoseToPoint incidences of one object's tracklets together (then by slot): the lanes of a
+    // warp in the Schur assembly then meet the same motion poses at the same step of their chain walks
+    std::vector<int> chain_group(n_chains, -1);
+    for (int64_t f = 0; f < n_ter; ++f) {
+      int& grp = chain_group[chain_of_point[in_ter_cur_[f]]];
+      if (grp >= 0) continue;
+      const Key key = pose_keys_[in_ter_motion_[f]];
+      const unsigned char ch = key_chr(key);
+      grp = (ch == kObjectMotionSymbolChar || ch == kObjectPoseSymbolChar) ? (int)key_label(key) : 256 + in_ter_motion_[f];
+    }
+    // ... and, within an object, by how far the point sits from its chain head (the length of the head-ward walk), so
+    // that the lanes of a warp finish their walks together
+    auto depth = [&](int slot) { return (slot - slice_base[chain_of_point[slot_point_[slot]] >> 5]) >> 5; };
+    for (int a = 0; a < np; ++a)
+      std::stable_sort(pp_idx.begin() + pp_ptr[a], pp_idx.begin() + pp_ptr[a + 1], [&](int e1, int e2) {
+        const int g1 = chain_group[chain_of_point[slot_point_[p2p_slot[e1]]]], g2 = chain_group[chain_of_point[slot_point_[p2p_slot[e2]]]];
+        return g1 != g2 ? g1 < g2 : depth(p2p_slot[e1]) > depth(p2p_slot[e2]);
+      });
+    build_csr(n_slots, [&](int s) { return ter_motion[s]; }, [&](int s) { return s; }, pt_ptr, pt_idx);
+    for (int a = 0; a < np; ++a)
+      std::stable_sort(pt_idx.begin() + pt_ptr[a], pt_idx.begin() + pt_ptr[a + 1], [&](int s1, int s2) { return depth(s1) > depth(s2); });
+  }
   build_csr(2 * n_btw, [&](int i) { return (i & 1) ? h_btw_b_[i >> 1] : h_btw_a_[i >> 1]; }, [&](int i) { return i; }, pb_ptr, pb_idx);
   build_csr(n_pri, [&](int i) { return h_pri_a_[i]; }, [&](int i) { return i; }, pr_ptr, pr_idx);
 
