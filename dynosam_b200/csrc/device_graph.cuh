@@ -112,6 +112,7 @@ struct BandSystem {
   double* S = nullptr;             // n_pad * ld
   double* y = nullptr;             // n_pad, right-hand side / solution in time order
   double* z = nullptr;             // n_pad, L^-1 rhs carried along by the factorisation
+  double* rdiag = nullptr;         // n_pad, reciprocals of the factor's diagonal
   double* Linv = nullptr;          // [n_pad / 64][64 x 64] inverses of the diagonal blocks of the factor
   long long* prof = nullptr;       // optional [8] ns counters of the factorisation phases (verbose >= 3)
   const int* first64 = nullptr;    // [n_pad / 64] smallest first envelope column over each group of 64 rows

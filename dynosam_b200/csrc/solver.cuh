@@ -232,7 +232,7 @@ class LmSolver {
   // direct reduced solve
   BandSystem band_;
   DevBuf<int> d_pose_pos_, d_pos_pose_, d_row_first_, d_first64_, d_fwd_min_;
-  DevBuf<double> d_S_, d_y_, d_zb_, d_Linv_, d_G_, d_res_;
+  DevBuf<double> d_S_, d_y_, d_zb_, d_Linv_, d_rdiag_, d_G_, d_res_;
   DevBuf<long long> d_prof_;
   bool band_ok_ = false, band_dirty_ = true, dpt_valid_ = false;
   int chol_grid_ = 0, back_grid_ = 0, assemble_smem_ = 0;
