@@ -152,6 +152,26 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def aggregate_over_ranks(dist, maxima, sums, device):
+    """Whole-job numbers from per-rank ones: times are the MAX over ranks (the job ends when the slowest replica
+    does), counts are SUMMED. `dist` is torch.distributed (initialised) or None for a single process."""
+    if dist is None:
+        return list(maxima), list(sums)
+    import torch
+    v = torch.tensor(list(maxima), dtype=torch.float64, device=device)
+    dist.all_reduce(v, op=dist.ReduceOp.MAX)
+    c = torch.tensor(list(sums), dtype=torch.float64, device=device)
+    dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    return [float(x) for x in v.tolist()], [float(x) for x in c.tolist()]
+
+
+def replica_config(workload, rank):
+    """N > 1 runs one independent scene of the workload's shape per GPU (multi-GPU): same sizes, own seed."""
+    cfg = dict(WORKLOADS[workload])
+    cfg["seed"] = cfg["seed"] + rank
+    return cfg
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -163,9 +183,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    cfg = dict(WORKLOADS[args.workload])
-    cfg["seed"] = cfg["seed"] + rank   # N > 1: independent replicas of the same shape (multi-GPU)
-    scene, g = build_graph(cfg)
+    scene, g = build_graph(replica_config(args.workload, rank))
     p = lm_params(local_rank)
     lm = d.GpuLevenbergMarquardt(g, p)
 
@@ -213,13 +231,8 @@ def run_ours(args, rank, world, local_rank):
     del e2e_lm
 
     # ---- aggregate over ranks ----
-    if dist is not None:
-        v = torch.tensor([dev_ms, wall_ms, e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(v, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms, e2e_s = (float(x) for x in v.tolist())
-        c = torch.tensor([iters, launches, e2e_iters], dtype=torch.float64, device="cuda")
-        dist.all_reduce(c, op=dist.ReduceOp.SUM)
-        iters, launches, e2e_iters = (int(x) for x in c.tolist())
+    (dev_ms, wall_ms, e2e_s), counts = aggregate_over_ranks(dist, (dev_ms, wall_ms, e2e_s), (iters, launches, e2e_iters), "cuda")
+    iters, launches, e2e_iters = (int(x) for x in counts)
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
