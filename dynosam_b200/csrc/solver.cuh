@@ -125,6 +125,42 @@ class LmSolver {
       in_ter_order_.push_back(order ? order[i] : -1);
     }
   }
+  // per-factor noise variants: one call for a whole flattened graph with mixed noise models (static / dynamic points)
+  int noise_group_cached(double sigma, double huber, double& last_s, double& last_h, int& last_g) {
+    if (last_g < 0 || sigma != last_s || huber != last_h) { last_g = noise_group(sigma, huber); last_s = sigma; last_h = huber; }
+    return last_g;
+  }
+  void add_p2p_v(int64_t n, const int32_t* pose, const int32_t* point, const double* z, const double* sigma, const double* huber, const int32_t* order) {
+    need_vars();
+    if (n < 0 || (n && (!pose || !point || !z || !sigma))) throw ArgError("add_pose_to_point_v: null or negative argument");
+    const int np = (int)pose_keys_.size(), npt = (int)point_keys_.size();
+    const size_t base = in_p2p_pose_.size();
+    in_p2p_pose_.resize(base + n); in_p2p_point_.resize(base + n); in_p2p_group_.resize(base + n); in_p2p_order_.resize(base + n);
+    in_p2p_z_.resize(3 * (base + n));
+    double ls = 0, lh = 0; int lg = -1;
+    for (int64_t i = 0; i < n; ++i) in_p2p_group_[base + i] = (unsigned char)noise_group_cached(sigma[i], huber ? huber[i] : 0.0, ls, lh, lg);
+    int bad = -1;
+#pragma omp parallel for schedule(static) reduction(max : bad)
+    for (int64_t i = 0; i < n; ++i) {
+      if (pose[i] < 0 || pose[i] >= np || point[i] < 0 || point[i] >= npt) bad = std::max(bad, (int)i);
+      in_p2p_pose_[base + i] = pose[i]; in_p2p_point_[base + i] = point[i];
+      in_p2p_z_[3 * (base + i)] = z[3 * i]; in_p2p_z_[3 * (base + i) + 1] = z[3 * i + 1]; in_p2p_z_[3 * (base + i) + 2] = z[3 * i + 2];
+      in_p2p_order_[base + i] = order ? order[i] : -1;
+    }
+    if (bad >= 0) { check_pose(pose[bad]); check_point(point[bad]); }
+  }
+  void add_ternary_v(int64_t n, const int32_t* prev, const int32_t* cur, const int32_t* motion, const double* sigma, const double* huber, const int32_t* order) {
+    need_vars();
+    if (n < 0 || (n && (!prev || !cur || !motion || !sigma))) throw ArgError("add_motion_ternary_v: null or negative argument");
+    double ls = 0, lh = 0; int lg = -1;
+    for (int64_t i = 0; i < n; ++i) {
+      check_point(prev[i]); check_point(cur[i]); check_pose(motion[i]);
+      if (prev[i] == cur[i]) throw ArgError("ternary factor with identical points");
+      in_ter_prev_.push_back(prev[i]); in_ter_cur_.push_back(cur[i]); in_ter_motion_.push_back(motion[i]);
+      in_ter_group_.push_back((unsigned char)noise_group_cached(sigma[i], huber ? huber[i] : 0.0, ls, lh, lg));
+      in_ter_order_.push_back(order ? order[i] : -1);
+    }
+  }
   void add_between(int64_t n, const int32_t* a, const int32_t* b, const double* z, const double* sig, const int32_t* order) {
     need_vars();
     if (n < 0 || (n && (!a || !b || !z)) || !sig) throw ArgError("add_between: null or negative argument");

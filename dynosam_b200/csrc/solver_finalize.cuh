@@ -136,6 +136,34 @@ inline void LmSolver::finalize() {
     for (int sl = 0; sl < n_slices; ++sl) max_depth = std::max(max_depth, slice_len[sl]);
     auto chain_of_slot = [&](int slot) { return slot_chain[slot]; };
     auto depth = [&](int slot) { return (slot - slice_base[slot_chain[slot] >> 5]) >> 5; };
+    // CSR in insertion order first (two linear passes), then every pose list is sorted on its own, in parallel, by
+    // (object, depth descending, insertion rank): the rank makes the order total, hence deterministic
+    pp_ptr.assign(np + 1, 0);
+    for (int e = 0; e < n_entries; ++e) if (p2p_pose[e] >= 0) pp_ptr[p2p_pose[e] + 1]++;
+    for (int a = 0; a < np; ++a) pp_ptr[a + 1] += pp_ptr[a];
+    std::vector<unsigned long long> pp_key(pp_ptr[np]);
+    {
+      std::vector<int> cur(pp_ptr.begin(), pp_ptr.end() - 1);
+      for (int e = 0; e < n_entries; ++e) {
+        if (p2p_pose[e] < 0) continue;
+        const int slot = p2p_slot[e];
+        const unsigned long long key = ((unsigned long long)chain_group[chain_of_slot(slot)] << 44) | ((unsigned long long)(max_depth - 1 - depth(slot)) << 28);
+        const int at = cur[p2p_pose[e]]++;
+        pp_key[at] = key | (unsigned long long)(at - pp_ptr[p2p_pose[e]]);   // low 28 bits: rank within the pose (insertion order)
+      }
+    }
+    pp_idx.assign(pp_ptr[np], 0);
+    {
+      // entry of (pose, rank): recover it from a second insertion-order pass
+      std::vector<int> by_rank(pp_ptr[np]);
+      std::vector<int> cur(pp_ptr.begin(), pp_ptr.end() - 1);
+      for (int e = 0; e < n_entries; ++e) if (p2p_pose[e] >= 0) by_rank[cur[p2p_pose[e]]++] = e;
+#pragma omp parallel for schedule(dynamic, 16)
+      for (int a = 0; a < np; ++a) {
+        std::sort(pp_key.begin() + pp_ptr[a], pp_key.begin() + pp_ptr[a + 1]);
+        for (int i = pp_ptr[a]; i < pp_ptr[a + 1]; ++i) pp_idx[i] = by_rank[pp_ptr[a] + (int)(pp_key[i] & 0xfffffffull)];
+      }
+    }
     // stable counting sort of `items` by key(item) in [0, n_keys)
     auto counting_sort = [&](std::vector<int>& items, int n_keys, auto key) {
       std::vector<int> start(n_keys + 1, 0), out(items.size());
@@ -144,16 +172,6 @@ inline void LmSolver::finalize() {
       for (int it : items) out[start[key(it)]++] = it;
       items.swap(out);
     };
-    std::vector<int> ent;
-    ent.reserve(n_p2p);
-    for (int e = 0; e < n_entries; ++e) if (p2p_pose[e] >= 0) ent.push_back(e);
-    counting_sort(ent, max_depth, [&](int e) { return max_depth - 1 - depth(p2p_slot[e]); });
-    counting_sort(ent, n_groups, [&](int e) { return chain_group[chain_of_slot(p2p_slot[e])]; });
-    pp_ptr.assign(np + 1, 0);
-    for (int e : ent) pp_ptr[p2p_pose[e] + 1]++;
-    for (int a = 0; a < np; ++a) pp_ptr[a + 1] += pp_ptr[a];
-    pp_idx.assign(pp_ptr[np], 0);
-    { std::vector<int> cur(pp_ptr.begin(), pp_ptr.end() - 1); for (int e : ent) pp_idx[cur[p2p_pose[e]]++] = e; }
     // ternary incidences of a motion pose: deepest first
     std::vector<int> ts;
     ts.reserve(n_ter);
