@@ -408,6 +408,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
     }
     if (tid < 64) { zs[tid] = bs.z[j0 + tid]; rd[tid] = bs.rdiag[j0 + tid]; }
     __syncthreads();
+    if (prof) { const long long t = gtime_ns(); sub_t[0] += t - t0; }
     for (int i = i_first; i < i_end; i += nwarp) {
       double* rowp = S + (size_t)i * ld + (j0 - i + bw);
       double v0, v1;
@@ -418,6 +419,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
       const double dot = warp_sum(v0 * zs[lane] + v1 * zs[lane + 32]);
       if (lane == 0) bs.y[i] -= dot;
     }
+    if (prof) { const long long t = gtime_ns(); sub_t[1] += t - t0; }
     __syncthreads();
     lap(0);
     grid.sync();
@@ -450,7 +452,8 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
     lap(3);
   }
   if (prof) for (int k = 0; k < 4; ++k) bs.prof[4 * blockIdx.x + k] = acc_t[k];
-  if (prof && blockIdx.x == 0) { bs.prof[8] = sub_t[3]; for (int k = 0; k < 23; ++k) bs.prof[9 + k] = dsub[k]; }
+  if (prof && blockIdx.x == 0) bs.prof[8] = sub_t[3];
+  if (prof && blockIdx.x == 1) { bs.prof[9] = sub_t[0]; bs.prof[10] = sub_t[1]; }
 }
 
 // Backward substitution x = L^-T z after k_band_cholesky (which left z = L^-1 rhs and the inverses of the

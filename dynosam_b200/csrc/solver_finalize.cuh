@@ -59,8 +59,8 @@ inline void LmSolver::finalize() {
     n_slots += slice_len[s] * 32;
   }
   slot_point_.assign(n_slots, -1); point_slot_.assign(npt, -1);
-  std::vector<int> ter_motion(n_slots, -1);
-  std::vector<unsigned char> ter_group(n_slots, 0);
+  auto& ter_motion = hs_ter_motion_; ter_motion.assign(n_slots, -1);
+  auto& ter_group = hs_ter_group_; ter_group.assign(n_slots, 0);
   ter_slot_of_input_.assign(n_ter, -1);
   std::vector<int> chain_of_point(npt, -1), slot_chain(n_slots, -1);
 #pragma omp parallel for schedule(static)
@@ -91,9 +91,13 @@ inline void LmSolver::finalize() {
   }
   for (int r = 0; r < n_rows; ++r) row_base[r + 1] += row_base[r];
   const int n_entries = row_base[n_rows];
-  std::vector<int> p2p_pose(n_entries, -1), p2p_slot(n_entries, -1), fill(npt, 0);
-  std::vector<unsigned char> p2p_group(n_entries, 0);
-  std::vector<double> zx(n_entries, 0.0), zy(n_entries, 0.0), zz(n_entries, 0.0);
+  std::vector<int> fill(npt, 0);
+  auto& p2p_pose = hs_p2p_pose_; p2p_pose.assign(n_entries, -1);
+  auto& p2p_slot = hs_p2p_slot_; p2p_slot.assign(n_entries, -1);
+  auto& p2p_group = hs_p2p_group_; p2p_group.assign(n_entries, 0);
+  auto& zx = hs_zx_; zx.assign(n_entries, 0.0);
+  auto& zy = hs_zy_; zy.assign(n_entries, 0.0);
+  auto& zz = hs_zz_; zz.assign(n_entries, 0.0);
   p2p_entry_of_input_.assign(n_p2p, -1);
   std::vector<int> rank(n_p2p);   // position of a factor among the factors of its point, in insertion order
   for (int64_t f = 0; f < n_p2p; ++f) rank[f] = fill[in_p2p_point_[f]]++;
@@ -206,7 +210,8 @@ inline void LmSolver::finalize() {
   d_pose_pri_ptr_.upload(pr_ptr, stream_); d_pose_pri_idx_.upload(pr_idx, stream_);
   d_p2p_entry_of_input_.upload(p2p_entry_of_input_, stream_); d_ter_slot_of_input_.upload(ter_slot_of_input_, stream_);
   // state
-  std::vector<double> pt4((size_t)n_slots * 4, 0.0);
+  auto& pt4 = hs_pt4_; pt4.assign((size_t)n_slots * 4, 0.0);
+#pragma omp parallel for schedule(static)
   for (int s = 0; s < n_slots; ++s) {
     const int pt = slot_point_[s];
     if (pt >= 0) { pt4[4 * (size_t)s] = h_point_[3 * (size_t)pt]; pt4[4 * (size_t)s + 1] = h_point_[3 * (size_t)pt + 1]; pt4[4 * (size_t)s + 2] = h_point_[3 * (size_t)pt + 2]; }
