@@ -34,7 +34,10 @@ WORKLOADS = {
     # BASELINE config 2: OMD-like, 4 objects, 500 frames, ~200k measurements
     "cfg2": dict(seed=1002),
 }
+# BASELINE config 4: sliding window W = 25 over the cfg3 scene, 300 windows, step 3 (overlap 22: BASELINE gives none, builder's choice)
+WINDOW, OVERLAP, N_WINDOWS = 25, 22, 300
 WORKLOAD_NAMES = {
+    "cfg4": "sliding window W=25 (step 3) x 300 windows over the KITTI-tracking-shaped scene, each re-built with a first-pose prior",
     "cfg3": "KITTI-tracking-shaped synthetic RGB-D scene (20 objects, 1000 frames, ~1.5M measurements), full batch",
     "cfg2": "OMD swinging_4_unconstrained-shaped synthetic scene (4 rigid objects, 500 frames, ~200k measurements), full batch",
 }
@@ -305,18 +308,92 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_windows(args, rank, world, local_rank):
+    """--workload cfg4: the reference's shipped default (RGBDBackendModule.cc:280-383): per window, rebuild the graph from the
+    measurements of frames [k-W, k] with a prior on the first pose, run LM to convergence with default parameters."""
+    import numpy as np
+    import torch
+    import dynosam_b200 as d
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; dynosam_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    scene = d.Scene.synthetic(**WORKLOADS["cfg3"])
+    sched = d.sliding_window_schedule(WINDOW, OVERLAP, 0, WORKLOADS["cfg3"]["n_frames"] - 1)[:N_WINDOWS]
+    mine = sched[rank::world]            # windows are independent solves: sharded over ranks, no data-path collective
+    p = d.default_lm_params()            # the reference runs default LevenbergMarquardtParams per window
+    p.device = local_rank
+    lm = d.GpuLevenbergMarquardt(None, p)
+
+    def one_pass(record):
+        dev_ms, iters, launches, lat, factors = 0.0, 0, 0, [], 0
+        for (a, b) in mine:
+            t0 = time.perf_counter()
+            g = scene.window_graph(a, b, True)
+            lm.load_graph(g)
+            lm.optimize()
+            lat.append(1e3 * (time.perf_counter() - t0))
+            t = lm.timing()
+            dev_ms += t["optimize_ms"]; iters += lm.iterations(); launches += int(t["kernel_launches"]); factors += g.n_factors
+        return dev_ms, iters, launches, lat, factors
+
+    for _ in range(args.warmup):
+        one_pass(False)
+    sampler = ClockSampler(local_rank)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    dev_ms, iters, launches, lat, factors = 0.0, 0, 0, [], 0
+    for _ in range(args.steps):
+        r = one_pass(True)
+        dev_ms += r[0]; iters += r[1]; launches += r[2]; lat += r[3]; factors += r[4]
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    wall_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    (dev_ms, wall_s, p99, p50), counts = aggregate_over_ranks(dist, (dev_ms, wall_s, float(np.percentile(lat, 99)), float(np.percentile(lat, 50))),
+                                                                (iters, launches, len(lat), factors), "cuda")
+    iters, launches, n_solved, factors = (int(x) for x in counts)
+    if rank == 0:
+        line = {
+            "metric": "sliding-window LM iterations/s", "value": iters / (dev_ms * 1e-3), "unit": "iter/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * wall_s / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD_NAMES["cfg4"], "formulation": "MotionInWorld (world-centric)", "window": WINDOW, "overlap": OVERLAP,
+                       "windows_per_step": len(sched), "mean_factors_per_window": factors / max(n_solved, 1), "lm": "default LevenbergMarquardtParams, to convergence",
+                       "l2": "each window is a new graph (flattened and uploaded inside the timed region)",
+                       "parallelism": "1 GPU" if world == 1 else "windows sharded over %d GPUs, no data-path collective" % world},
+            "clocks": clocks,
+            "e2e": {"value": iters / wall_s, "unit": "iter/s", "windows_per_s": n_solved / wall_s, "note": "host graph construction (constructGraph mirror) + flattening + H2D + optimize + D2H per window"},
+            "window_latency_ms": {"p50": p50, "p99": p99, "note": "max over ranks of the per-rank percentiles"},
+            "gpu_launches": launches, "mean_lm_iterations_per_window": iters / max(n_solved, 1),
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + ["cfg4"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
+        if args.workload == "cfg4":
+            raise SystemExit("bench.py: the CPU arm is defined for the full-batch workloads only")
         run_reference(args, rank)
+    elif args.workload == "cfg4":
+        run_windows(args, rank, world, local_rank)
     else:
         run_ours(args, rank, world, local_rank)
 

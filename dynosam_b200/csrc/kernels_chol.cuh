@@ -462,7 +462,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
 // the z entries of the window columns left of the panel, one column per thread (row-panel reads are contiguous).
 // x is written in natural pose order. z is consumed.
 constexpr int kBackThreads = 256;
-__global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, double* __restrict__ x) {
+__global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, double* __restrict__ x, int add_to_x) {
   cg::grid_group grid = cg::this_grid();
   __shared__ double part[4][64];
   __shared__ double xs[64];
@@ -508,7 +508,11 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
       const double v = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
       xs[tid] = v;
       const int i = j0 + tid;
-      if (blockIdx.x == 0 && i < bs.n) { const int p = i / 6, cc = i - 6 * p; x[6 * (size_t)bs.pos_pose[p] + cc] = v; }
+      if (blockIdx.x == 0 && i < bs.n) {
+        const int p = i / 6, cc = i - 6 * p;
+        double* dst = x + 6 * (size_t)bs.pos_pose[p] + cc;
+        *dst = add_to_x ? *dst + v : v;
+      }
     }
     __syncthreads();
     if (c >= 0) {
@@ -526,6 +530,80 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
         c = c1;
       }
       prefetch(j1, c);                          // in flight across the barrier
+    }
+    grid.sync();
+  }
+}
+
+// Forward substitution z = L^-1 y for a right-hand side that did not ride along with the factorisation (iterative
+// refinement). Mirror image of k_band_backsolve: same grid, one barrier per panel, every CTA forms z_J = Linv_J y_J,
+// then the thread that owns row i of the window below the panel subtracts L[i, J] z_J from its y_i (kept in a
+// register while the panels approach the row; the 64 entries of L it needs are contiguous). y is consumed.
+__global__ void __launch_bounds__(kBackThreads) k_band_fwdsolve(BandSystem bs) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double Ls[64 * 65];
+  __shared__ double part[4][64];
+  __shared__ double zs[64];
+  const int tid = threadIdx.x;
+  const size_t ld = bs.ld;
+  const int bw = bs.bw;
+  const double* __restrict__ S = bs.S;
+  double* __restrict__ y = bs.y;
+  const int gtid = blockIdx.x * kBackThreads + tid, gsize = gridDim.x * kBackThreads;   // gsize >= window + 64
+  auto row_of = [&](int j0) {
+    int d = (gtid - (j0 + 64)) % gsize;
+    if (d < 0) d += gsize;
+    const int i = j0 + 64 + d;
+    return (i < bs.n_pad && d < bs.window) ? i : -1;
+  };
+  const int k = tid & 63, pt = tid >> 6;
+  double lr[64], li[16];
+  auto prefetch = [&](int j0, int i) {
+    const double* Li = bs.Linv + (size_t)(j0 >> 6) * 4096;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) li[q] = Li[tid + 256 * q];
+    if (i >= 0) {
+      const double* row = S + (size_t)i * ld + (j0 - i + bw);
+#pragma unroll
+      for (int rr = 0; rr < 64; ++rr) lr[rr] = row[rr];
+    }
+  };
+  int j0 = 0;
+  int i = row_of(j0);
+  double yreg = i >= 0 ? y[i] : 0.0;
+  prefetch(j0, i);
+  for (; j0 < bs.n_pad; j0 += 64) {
+#pragma unroll
+    for (int q = 0; q < 16; ++q) { const int e = tid + 256 * q; Ls[(e >> 6) * 65 + (e & 63)] = li[q]; }
+    __syncthreads();
+    {  // z_k = sum_{m <= k} Linv[k][m] y_m
+      double s = 0.0;
+#pragma unroll
+      for (int mm = 0; mm < 16; ++mm) s = fma(Ls[k * 65 + pt * 16 + mm], y[j0 + pt * 16 + mm], s);
+      part[pt][k] = s;
+    }
+    __syncthreads();
+    if (tid < 64) {
+      const double v = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
+      zs[tid] = v;
+      if (blockIdx.x == 0) bs.z[j0 + tid] = v;
+    }
+    __syncthreads();
+    if (i >= 0) {
+      double s = 0.0;
+#pragma unroll
+      for (int rr = 0; rr < 64; ++rr) s = fma(lr[rr], zs[rr], s);
+      yreg -= s;
+    }
+    const int j1 = j0 + 64;
+    if (j1 < bs.n_pad) {
+      const int i1 = row_of(j1);
+      if (i1 != i) {
+        if (i >= 0) y[i] = yreg;               // row i joins the next panel: publish before the barrier
+        yreg = i1 >= 0 ? y[i1] : 0.0;          // untouched so far
+        i = i1;
+      }
+      prefetch(j1, i);
     }
     grid.sync();
   }

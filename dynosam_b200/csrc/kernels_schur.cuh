@@ -155,7 +155,8 @@ __global__ void __launch_bounds__(kSchurThreads, 4) k_schur_assemble_warp(Device
   const int n1 = g.pose_p2p_ptr[a + 1] - g.pose_p2p_ptr[a];
   const int n2 = g.pose_ter_ptr[a + 1] - g.pose_ter_ptr[a];
   M3 Rt; { M3 Ra; _Pragma("unroll") for (int i = 0; i < 9; ++i) Ra.a[i] = pose_lin[12 * (size_t)a + i]; Rt = m3_t(Ra); }
-  for (int base = wid * 32; base < n1 + n2; base += nw * 32) {
+  // a pose's incidences are dealt out in chunks of 32 to the warps of gridDim.y CTAs (small graphs have few, heavy poses)
+  for (int base = (blockIdx.y * nw + wid) * 32; base < n1 + n2; base += nw * 32 * gridDim.y) {
     const int t = base + lane;
     const bool valid = t < n1 + n2;
     const bool is_ter = valid && t >= n1;

@@ -366,6 +366,7 @@ inline void LmSolver::setup_band(const std::vector<int>& chain_of_point) {
   if (per_sm < 1) throw CudaError("k_band_cholesky does not fit on an SM");
   back_grid_ = (band_.window + 64 + kBackThreads - 1) / kBackThreads;   // one thread per column of window + panel
   if (back_grid_ > sms) throw CudaError("band window too wide for the cooperative back-substitution");
+  schur_split_ = std::min(16, std::max(1, (8 * sms + np - 1) / np));   // about 8 assembly CTAs per SM in flight even for a window of a few hundred poses
   chol_grid_ = sms;   // one persistent CTA per SM: CTA 0 runs the serial chain, the others 4 tile groups each
   band_ok_ = true;
   timing_[18] = (double)bytes;
