@@ -135,8 +135,7 @@ def run_reference(args, rank):
         return
     import oracle_lib
     oracle_lib.build()
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = set_host_threads(os.cpu_count() or 1)   # rank 0 alone runs: all host cores
     _, full = build_graph(WORKLOADS[args.workload])
     g, times, iters = cpu_oracle_run(args.steps, args.warmup)
     per_iter_sample = sum(times) / max(iters, 1)
@@ -153,6 +152,25 @@ def run_reference(args, rank):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def set_host_threads(n):
+    """torchrun exports OMP_NUM_THREADS=1; the host flattening and the CPU oracle are OpenMP code and get the cores this
+    rank is entitled to. libgomp is already loaded (by torch), so the environment is not re-read: call into it."""
+    import ctypes
+    n = max(1, int(n))
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(n)
+    except OSError:
+        pass
+    return n
+
+
+def quiet_nccl():
+    # keep stdout to the one JSON line (a box-wide NCCL_DEBUG=VERSION prints a banner there)
+    if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+        os.environ["NCCL_DEBUG"] = "WARN"
 
 
 def aggregate_over_ranks(dist, maxima, sums, device):
@@ -182,8 +200,10 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; dynosam_b200 has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    set_host_threads((os.cpu_count() or 1) // world)
     dist = None
     if world > 1:
+        quiet_nccl()
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene, g = build_graph(replica_config(args.workload, rank))
@@ -280,6 +300,7 @@ def run_ours(args, rank, world, local_rank):
     # CPU baseline beside the GPU number (N = 1 only), bounded sample
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
+        set_host_threads(os.cpu_count() or 1)
         sg, times, it = cpu_oracle_run(1, 0)
         per_iter = sum(times) / max(it, 1)
         scale = g.n_factors / sg.n_factors
@@ -317,8 +338,10 @@ def run_windows(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; dynosam_b200 has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    set_host_threads((os.cpu_count() or 1) // world)
     dist = None
     if world > 1:
+        quiet_nccl()
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     scene = d.Scene.synthetic(**WORKLOADS["cfg3"])

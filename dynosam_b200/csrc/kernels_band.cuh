@@ -2,14 +2,13 @@
 //
 //   S = A_pp + lambda I - W^T (M + lambda I)^-1 W      (poses in time order, lower band storage)
 //
-//   k_schur_assemble : one CTA per pose row. Every factor incidence of the pose walks its point
+//   k_schur_init / k_schur_assemble_warp (kernels_schur.cuh): every factor incidence of a pose walks its point
 //                      chain (a static landmark is a chain of one point, a dynamic tracklet a
 //                      block-tridiagonal chain) with the selected-inverse recursion and adds
-//                      W_a^T Sigma_{i,q} W_{q,u} for every pose u of the chain that is not later
-//                      than a. The row is accumulated in shared memory (shared-memory atomics
-//                      only) and streamed to HBM once: no global atomics.
-//   k_band_cholesky  : cooperative right-looking blocked Cholesky of the band, in place.
-//   k_band_solve     : forward + backward substitution with the band factor.
+//                      W_a^T Sigma_{i,q} W_{q,u} for every pose u of the chain that is not later than a.
+//   k_band_cholesky  : cooperative right-looking blocked Cholesky of the band, in place, carrying L^-1 rhs (kernels_chol.cuh).
+//   k_band_backsolve / k_band_fwdsolve : cooperative substitutions with the band factor (kernels_chol.cuh).
+// This file keeps the small 6x3 block helpers they share and a few utility kernels.
 //
 // This is what GTSAM's multifrontal Cholesky does for the reference on the CPU
 // (LevenbergMarquardtOptimizer::tryLambda -> solve(dampedSystem), reference call site
@@ -55,230 +54,7 @@ __device__ __forceinline__ void t63_mul_s3(double* O, const double* U, const S3&
   }
 }
 
-// acc block (6 x 6 at column 6*lb of the row accumulator) -= w * T * [ sgn * R^T-rotated form ]:
-//   rotated = true : row r of the product is w * [ (tr x q) | -tr ],  tr = R^T t_r      (PoseToPoint pose block
-//                    w R [[q]x | -I], and the current-point side of a ternary factor -w R_H [-[q]x | I])
-//   rotated = false: row r is w * [ -(t_r x q) | t_r ]                                    (previous-point side, w [-[q]x | I])
-__device__ __forceinline__ void acc_sub_block(double* acc, int ncol, int lb, const double* T, bool rotated, const M3& R, V3 q, double w) {
-  double* base = acc + 6 * lb;
-#pragma unroll
-  for (int r = 0; r < 6; ++r) {
-    V3 t = v3(T[3 * r], T[3 * r + 1], T[3 * r + 2]);
-    double sgn = -w;
-    if (rotated) { t = m3_apply_t(R, t); sgn = w; }
-    const V3 c = cross3(t, q);
-    double* row = base + (size_t)r * ncol;
-    atomicAdd(row + 0, -sgn * c.x); atomicAdd(row + 1, -sgn * c.y); atomicAdd(row + 2, -sgn * c.z);
-    atomicAdd(row + 3, sgn * t.x);  atomicAdd(row + 4, sgn * t.y);  atomicAdd(row + 5, sgn * t.z);
-  }
-}
 
-// every factor touching point slot q contributes T_q * W_{q,u} to block (a, u) when pos[u] <= p
-__device__ __forceinline__ void schur_emit(const DeviceGraph& g, const BandSystem& bs, int p, int first, double* acc, int ncol,
-                                           const double* __restrict__ pose_lin, const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
-                                           int q, const double* T) {
-  const int row = q >> 5, lane = q & 31;
-  const int e0 = g.row_base[row], deg = (g.row_base[row + 1] - e0) >> 5;
-  for (int j = 0; j < deg; ++j) {
-    const int e = e0 + j * 32 + lane;
-    const int u = g.p2p_pose[e];
-    if (u < 0) continue;
-    const int pu = bs.pose_pos[u];
-    if (pu > p) continue;
-    const double4 c = p2p_qw[e];
-    M3 R; for (int i = 0; i < 9; ++i) R.a[i] = pose_lin[12 * (size_t)u + i];
-    acc_sub_block(acc, ncol, pu - first, T, true, R, v3(c.x, c.y, c.z), c.w);
-  }
-  const int h = g.ter_motion[q];
-  if (h >= 0) {  // q is the current point of factor (q-32, q, h)
-    const int pu = bs.pose_pos[h];
-    if (pu <= p) {
-      const double4 c = ter_qw[q];
-      M3 R; for (int i = 0; i < 9; ++i) R.a[i] = pose_lin[12 * (size_t)h + i];
-      acc_sub_block(acc, ncol, pu - first, T, true, R, v3(c.x, c.y, c.z), c.w);
-    }
-  }
-  const int nxt = q + 32;
-  const int h2 = (nxt < g.n_slots) ? g.ter_motion[nxt] : -1;
-  if (h2 >= 0) {  // q is the previous point of factor (q, q+32, h2)
-    const int pu = bs.pose_pos[h2];
-    if (pu <= p) {
-      const double4 c = ter_qw[nxt];
-      M3 R; R.a[0] = 0;
-      acc_sub_block(acc, ncol, pu - first, T, false, R, v3(c.x, c.y, c.z), c.w);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(256) k_schur_assemble(DeviceGraph g, BandSystem bs, double lambda, const double* __restrict__ pose_lin,
-                                                        const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
-                                                        const int* __restrict__ p2p_slot, const double* __restrict__ btw_J,
-                                                        const double* __restrict__ App, const double* __restrict__ Sig, const double* __restrict__ G) {
-  extern __shared__ double acc[];  // [6][ncol]
-  const int p = blockIdx.x;
-  const int a = bs.pos_pose[p];
-  const int first = bs.row_first[p];
-  const int ncol = 6 * (p - first + 1);
-  for (int i = threadIdx.x; i < 6 * ncol; i += blockDim.x) acc[i] = 0.0;
-  __syncthreads();
-  // diagonal block and the between factors whose other pose is earlier
-  if (threadIdx.x < 36) {
-    const int r = threadIdx.x / 6, c = threadIdx.x - 6 * r;
-    acc[(size_t)r * ncol + 6 * (p - first) + c] = App[36 * (size_t)a + threadIdx.x] + (r == c ? lambda : 0.0);
-  }
-  __syncthreads();
-  for (int k = g.pose_btw_ptr[a]; k < g.pose_btw_ptr[a + 1]; ++k) {
-    const int fr = g.pose_btw_idx[k];
-    const int f = fr >> 1, role = fr & 1;
-    const int o = role ? g.btw_a[f] : g.btw_b[f];
-    const int po = bs.pose_pos[o];
-    if (po >= p) continue;
-    if (threadIdx.x < 36) {
-      const int r = threadIdx.x / 6, c = threadIdx.x - 6 * r;
-      const double* rec = btw_J + 78 * (size_t)f;
-      const double* Jme = rec + (role ? 42 : 6);
-      const double* Jot = rec + (role ? 6 : 42);
-      double s = 0;
-      for (int m = 0; m < 6; ++m) s += Jme[6 * m + r] * Jot[6 * m + c];
-      acc[(size_t)r * ncol + 6 * (po - first) + c] += s;
-    }
-    __syncthreads();
-  }
-  __syncthreads();
-  // factor incidences of pose a: its PoseToPoint entries, and both point rows of each ternary factor it is the motion of
-  const int n1 = g.pose_p2p_ptr[a + 1] - g.pose_p2p_ptr[a];
-  const int n2 = g.pose_ter_ptr[a + 1] - g.pose_ter_ptr[a];
-  M3 Ra; for (int i = 0; i < 9; ++i) Ra.a[i] = pose_lin[12 * (size_t)a + i];
-  for (int t = threadIdx.x; t < n1 + 2 * n2; t += blockDim.x) {
-    int slot;
-    double Wt[18];  // W_i^T, 6x3 row-major:  W_i = (J_point^T J_pose) * w  (3x6)
-    if (t < n1) {
-      const int e = g.pose_p2p_idx[g.pose_p2p_ptr[a] + t];
-      slot = p2p_slot[e];
-      const double4 c = p2p_qw[e];
-      // W = w R [[q]x | -I]  =>  W^T = w [ -[q]x R^T ; -R^T ]
-      const M3 Rt = m3_t(Ra);
-      const M3 Q = m3_hat(v3(c.x, c.y, c.z));
-      const M3 QRt = m3_mul(Q, Rt);
-      for (int i = 0; i < 9; ++i) { Wt[i] = -c.w * QRt.a[i]; Wt[9 + i] = -c.w * Rt.a[i]; }
-    } else {
-      const int tt = t - n1;
-      const int s = g.pose_ter_idx[g.pose_ter_ptr[a] + (tt >> 1)];
-      const double4 c = ter_qw[s];
-      const M3 Q = m3_hat(v3(c.x, c.y, c.z));
-      if (tt & 1) {  // previous point row: W = w [-[q]x | I]  =>  W^T = w [ [q]x ; I ]
-        slot = s - 32;
-        for (int i = 0; i < 9; ++i) { Wt[i] = c.w * Q.a[i]; Wt[9 + i] = 0.0; }
-        Wt[9] = Wt[13] = Wt[17] = c.w;
-      } else {       // current point row: W = -w R [-[q]x | I]  =>  W^T = w [ -[q]x R^T ; -R^T ]
-        slot = s;
-        const M3 Rt = m3_t(Ra);
-        const M3 QRt = m3_mul(Q, Rt);
-        for (int i = 0; i < 9; ++i) { Wt[i] = -c.w * QRt.a[i]; Wt[9 + i] = -c.w * Rt.a[i]; }
-      }
-    }
-    double T[18];
-    t63_mul_s3(T, Wt, s3_load(Sig + 6 * (size_t)slot));
-    schur_emit(g, bs, p, first, acc, ncol, pose_lin, p2p_qw, ter_qw, slot, T);
-    // towards the chain head: T_{q-1} = T_q (-G_{q-1})^T, G_{q-1} stored at slot q
-    for (int q = slot; g.ter_motion[q] >= 0; q -= 32) {
-      t63_mul_mt(T, G + 9 * (size_t)q, -1.0);
-      schur_emit(g, bs, p, first, acc, ncol, pose_lin, p2p_qw, ter_qw, q - 32, T);
-    }
-    // towards the chain tail: U_{q+1} = U_q (-G_q), T_{q+1} = U_{q+1} Sigma_{q+1,q+1}
-    for (int q = slot + 32; q < g.n_slots && g.ter_motion[q] >= 0; q += 32) {
-      t63_mul_m(Wt, G + 9 * (size_t)q, -1.0);
-      t63_mul_s3(T, Wt, s3_load(Sig + 6 * (size_t)q));
-      schur_emit(g, bs, p, first, acc, ncol, pose_lin, p2p_qw, ter_qw, q, T);
-    }
-  }
-  __syncthreads();
-  // stream the row out: scalar row 6p+i holds columns 6*first .. 6p+i
-  for (int i = 0; i < 6; ++i) {
-    const size_t r = 6 * (size_t)p + i;
-    double* dst = bs.S + r * bs.ld + (6 * (size_t)first + bs.bw - r);
-    const int len = ncol - (5 - i);
-    for (int c = threadIdx.x; c < len; c += blockDim.x) dst[c] = acc[(size_t)i * ncol + c];
-  }
-}
-
-// x = L^-T L^-1 b with the band factor; b and x are in natural pose order (6 per pose), bs.y is scratch.
-// add_to_x: x += solution (iterative refinement) instead of x = solution. use_z: the forward substitution
-// was already carried along by the factorisation (bs.z = L^-1 rhs), only the backward half runs.
-// Single CTA of 1024 threads.
-__global__ void __launch_bounds__(1024) k_band_solve(BandSystem bs, int n_pose, const double* __restrict__ b, double* __restrict__ x, int add_to_x, int use_z) {
-  constexpr int NB = kSolveNB;
-  __shared__ double D[NB][NB + 1];
-  __shared__ double part[32][NB + 1];
-  __shared__ double rs[NB];
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const size_t ld = bs.ld;
-  const int bw = bs.bw;
-  const double* __restrict__ S = bs.S;
-  double* __restrict__ y = bs.y;
-  for (int i = tid; i < bs.n_pad; i += blockDim.x) {
-    double v = 0.0;
-    if (use_z) v = bs.z[i];
-    else if (i < bs.n) { const int p = i / 6, c = i - 6 * p; v = b[6 * (size_t)bs.pos_pose[p] + c]; }
-    y[i] = v;
-  }
-  __syncthreads();
-  // ---- forward: y_panel = L_jj^-1 (b_panel - L[panel, window before] y) ----
-  for (int j0 = 0; j0 < (use_z ? 0 : bs.n_pad); j0 += NB) {
-    for (int idx = tid; idx < NB * NB; idx += blockDim.x) {
-      const int r = idx / NB, c = idx - NB * r;
-      D[r][c] = (c <= r) ? S[(size_t)(j0 + r) * ld + (c - r + bw)] : 0.0;
-    }
-    {  // warp w <-> panel row w: dot product over the columns before the panel
-      const int i = j0 + wid;
-      const int c_lo = max(0, i - bw);
-      const double* rowp = S + (size_t)i * ld + (bw - i);
-      double s = 0.0;
-      for (int c = c_lo + lane; c < j0; c += 32) s += rowp[c] * y[c];
-      s = warp_sum(s);
-      if (lane == 0) rs[wid] = y[i] - s;
-    }
-    __syncthreads();
-    if (wid == 0) {
-      double v = rs[lane];
-      for (int m = 0; m < NB; ++m) {
-        const double xm = __shfl_sync(0xffffffffu, v, m) / D[m][m];
-        if (lane == m) v = xm;
-        else if (lane > m) v -= xm * D[lane][m];
-      }
-      y[j0 + lane] = v;
-    }
-    __syncthreads();
-  }
-  // ---- backward: x_panel = L_jj^-T (y_panel - L[window below, panel]^T x) ----
-  for (int j0 = bs.n_pad - NB; j0 >= 0; j0 -= NB) {
-    for (int idx = tid; idx < NB * NB; idx += blockDim.x) {
-      const int r = idx / NB, c = idx - NB * r;
-      D[r][c] = (c <= r) ? S[(size_t)(j0 + r) * ld + (c - r + bw)] : 0.0;
-    }
-    const int i_begin = j0 + NB, i_end = min(bs.n_pad, i_begin + bs.window);
-    double s = 0.0;
-    for (int i = i_begin + wid; i < i_end; i += 32) s += S[(size_t)i * ld + (j0 + lane - i + bw)] * y[i];
-    part[wid][lane] = s;
-    __syncthreads();
-    if (wid == 0) {
-      double v = y[j0 + lane];
-      for (int w = 0; w < 32; ++w) v -= part[w][lane];
-      for (int m = NB - 1; m >= 0; --m) {
-        const double xm = __shfl_sync(0xffffffffu, v, m) / D[m][m];
-        if (lane == m) v = xm;
-        else if (lane < m) v -= xm * D[m][lane];
-      }
-      y[j0 + lane] = v;
-    }
-    __syncthreads();
-  }
-  for (int i = tid; i < bs.n; i += blockDim.x) {
-    const int p = i / 6, c = i - 6 * p;
-    double* dst = x + 6 * (size_t)bs.pos_pose[p] + c;
-    *dst = add_to_x ? (*dst + y[i]) : y[i];
-  }
-}
 
 // FP64 FMA peak probe: 8 independent register chains per thread, 4096 FMAs each
 __global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters) {

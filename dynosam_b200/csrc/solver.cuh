@@ -318,7 +318,7 @@ class LmSolver {
   HostStage<unsigned char> hs_p2p_group_, hs_ter_group_;
   HostStage<double> hs_zx_, hs_zy_, hs_zz_, hs_pt4_;
   bool band_ok_ = false, band_dirty_ = true, dpt_valid_ = false;
-  int chol_grid_ = 0, back_grid_ = 0, assemble_smem_ = 0;
+  int chol_grid_ = 0, back_grid_ = 0;
   int schur_split_ = 1;   // CTAs per pose in the Schur assembly
   std::string band_why_not_;
 };

@@ -196,3 +196,27 @@ def test_host_array_handover_matches_graph_handover():
     assert b.error() == c.error()
     b.optimize(); c.optimize()
     assert np.allclose(b.error_trace, c.error_trace, rtol=1e-12, atol=0)
+
+
+def test_baseline_config2_size_matches_oracle():
+    """BASELINE config 2 at full size (OMD-like: 4 objects, 500 frames, ~200k measurements, seed 1002): chi^2, one damped
+    solve and a 3-iteration LM trace against the oracle; the reduced system is a 12k-wide band here."""
+    g = d.Scene.synthetic(seed=1002).full_batch_graph()
+    assert g.n_p2p > 150000
+    ora = OracleGraph.from_graph(g)
+    p = d.default_lm_params()
+    p.max_iterations = 3
+    p.relative_error_tol = 0.0
+    p.absolute_error_tol = 0.0
+    gpu = d.GpuLevenbergMarquardt(g, p)
+    e_gpu, e_cpu = gpu.error(), ora.error()
+    assert abs(e_gpu - e_cpu) <= 1e-12 * e_cpu
+    ok_g, dp_g, dpt_g, _ = gpu.solve_once(1e-5)
+    ok_c, dp_c, dpt_c = ora.solve_once(1e-5)
+    assert ok_g and ok_c
+    assert rel_err(dp_g, dp_c) <= 1e-6 and rel_err(dpt_g, dpt_c) <= 1e-6
+    gpu.optimize()
+    r = ora.optimize(max_iterations=3, relative_error_tol=0.0, absolute_error_tol=0.0)
+    assert gpu.iterations() == r["iterations"] and gpu.getInnerIterations() == r["inner_iterations"]
+    tr_g, tr_c = np.array(gpu.error_trace), np.array(r["error_trace"])
+    assert np.all(np.abs(tr_g - tr_c) <= CHI2_RTOL * np.abs(tr_c)), (tr_g, tr_c)

@@ -1,6 +1,6 @@
 """Dev script: where does the end-to-end (host buffers -> optimised values) time go?  python gpu_e2e.py [cfg3|cfg2]"""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import bench
 import dynosam_b200 as d

@@ -1,6 +1,6 @@
 """Dev script: phase times of one sliding-window solve (cfg4 shape)."""
 import os, sys, time
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 import dynosam_b200 as d
 scene = d.Scene.synthetic(**bench.WORKLOADS["cfg3"])
