@@ -42,16 +42,24 @@ __device__ __forceinline__ double fast_rsqrt(double d) {
   return y;
 }
 
+// 1/d to double precision (hardware f64 seed + two Newton steps): the only non-FMA operation on the serial chain of the
+// diagonal factorisation below
+__device__ __forceinline__ double fast_rcp(double d) {
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  y = y * fma(-d, y, 2.0);
+  y = y * fma(-d, y, 2.0);
+  return y;
+}
+
 // One warp factors the 32 x 32 SPD block A (shared memory, row stride 65, lower triangle) in place, lane = row.
 // Columns go in chunks of 8: a chunk is first brought up to date against the finished columns (left-looking, operands
 // from shared memory), then factored right-looking in registers with the pivot column travelling by shuffle. The
 // loops over chunks are rolled on purpose: this code sits on the factorisation's serial chain and is run by a single
 // warp, so it has to stay resident in the instruction cache (a fully unrolled 32-column version measured 4x slower).
 // The reciprocals of the diagonal go to rd[0..31]. Entries above the diagonal are scratch.
-__device__ __noinline__ void warp_chol32(double* __restrict__ A, int lane, double* __restrict__ rd, int* __restrict__ flags, long long* pt = nullptr) {
+__device__ __noinline__ void warp_chol32(double* __restrict__ A, int lane, double* __restrict__ rd, int* __restrict__ flags) {
   bool bad = false;
-  long long tw = (pt && lane == 0) ? clock64() : 0;
-  long long tw2 = tw;
 #pragma unroll 1
   for (int c0 = 0; c0 < 32; c0 += 8) {
     double a[8];
@@ -65,20 +73,20 @@ __device__ __noinline__ void warp_chol32(double* __restrict__ A, int lane, doubl
     }
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-      if (pt && lane == 0 && c0 == 0) { const long long t1 = clock64(); pt[8 + c] += t1 - tw2; tw2 = t1; }
       const double d = __shfl_sync(0xffffffffu, a[c], c0 + c);
       bad |= !(d > 0.0);
+      // trailing update with a[c] / d (one reciprocal on the chain); the column itself is scaled by 1/sqrt(d) off the chain:
+      // a_r[c2] -= L[r][c] L[c2][c] = a_r[c] a_c2[c] / d
+      const double t = a[c] * fast_rcp(d);
+#pragma unroll
+      for (int c2 = c + 1; c2 < 8; ++c2) a[c2] = fma(-t, __shfl_sync(0xffffffffu, a[c], c0 + c2), a[c2]);
       const double rk = fast_rsqrt(d);
       if (lane == c0 + c) rd[c0 + c] = rk;
-      const double lk = a[c] * rk;   // L[lane][c0 + c] (diagonal: d * rsqrt(d) = sqrt(d))
-      a[c] = lk;
-#pragma unroll
-      for (int c2 = c + 1; c2 < 8; ++c2) a[c2] = fma(-lk, __shfl_sync(0xffffffffu, lk, c0 + c2), a[c2]);
+      a[c] *= rk;   // L[lane][c0 + c] (diagonal: d * rsqrt(d) = sqrt(d))
     }
 #pragma unroll
     for (int c = 0; c < 8; ++c) A[lane * 65 + c0 + c] = a[c];
     __syncwarp();
-    if (pt && lane == 0) { const long long t1 = clock64(); pt[c0 >> 3] += t1 - tw; tw = t1; }
   }
   if (bad && lane == 0) atomicOr(flags, 4);
 }
@@ -174,13 +182,10 @@ __device__ __forceinline__ void chol_diag_tile(const BandSystem& bs, int j0, int
 // bs.rdiag and z[j0..j0+63] = L^-1 y[j0..j0+63]. 2 x 2 blocking: the two 32 x 32 factorisations run in the registers of
 // warp 0 (one code instance, looped), the 32 x 32 solve and update between them on the other warps.
 // D: 64 x 65 scratch, rd: 64, zs: 64. Not inlined: a single copy of this code per kernel.
-__device__ __noinline__ void chol_diag64(const BandSystem& bs, int j0, double* __restrict__ D, double* __restrict__ rd, double* __restrict__ zs, int* __restrict__ flags, long long* pt) {
+__device__ __noinline__ void chol_diag64(const BandSystem& bs, int j0, double* __restrict__ D, double* __restrict__ rd, double* __restrict__ zs, int* __restrict__ flags) {
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  long long tq = (pt && tid == 0) ? clock64() : 0;
-  auto lapd = [&](int slot) { if (pt && tid == 0) { const long long t1 = clock64(); pt[slot] += t1 - tq; tq = t1; } };
   const size_t ld = bs.ld;
   const int bw = bs.bw;
-  lapd(0);
 #pragma unroll 1
   for (int blk = 0; blk < 2; ++blk) {
     if (blk == 1) {
@@ -190,7 +195,6 @@ __device__ __noinline__ void chol_diag64(const BandSystem& bs, int j0, double* _
         zs[lane] = warp_fwd32(zs[lane], D, rd, lane);
       }
       __syncthreads();
-      lapd(2);
       // A22 -= L21 L21^T (thread: row i, two columns), y2 -= L21 z1; A22 and y2 are disjoint from the operands
       const int i = tid >> 4, j = (tid & 15) * 2;
       double s0 = 0.0, s1 = 0.0;
@@ -209,11 +213,9 @@ __device__ __noinline__ void chol_diag64(const BandSystem& bs, int j0, double* _
         zs[32 + tid] -= y2;
       }
       __syncthreads();
-      lapd(3);
     }
-    if (wid == 0) warp_chol32(D + blk * (32 * 65 + 32), lane, rd + 32 * blk, flags, (pt && blk == 1) ? pt + 6 : nullptr);   // L11, then L22
+    if (wid == 0) warp_chol32(D + blk * (32 * 65 + 32), lane, rd + 32 * blk, flags);   // L11, then L22
     __syncthreads();
-    lapd(blk == 0 ? 1 : 4);
   }
   if (wid == 0) {   // z2 = L22^-1 (y2 - L21 z1)
     zs[32 + lane] = warp_fwd32(zs[32 + lane], D + 32 * 65 + 32, rd + 32, lane);
@@ -227,7 +229,6 @@ __device__ __noinline__ void chol_diag64(const BandSystem& bs, int j0, double* _
   __syncthreads();
   if (tid < 64) bs.z[j0 + tid] = zs[tid];
   __syncthreads();
-  lapd(5);
 }
 
 // Inverses of the diagonal blocks of the factor (used by the backward substitution), one CTA of 256 threads per block,
@@ -282,7 +283,8 @@ __global__ void __launch_bounds__(256) k_band_diag_inverse(BandSystem bs) {
 }
 
 // element k (k = lane, lane + 32) of a 64-vector held as v0/v1 across a warp:  v <- v L^-T  (rows: x L^T = a),
-// L (64 x 64 lower, row stride 65) and the reciprocals of its diagonal in shared memory
+// L (64 x 64 lower, row stride 65) and the reciprocals of its diagonal in shared memory.
+// (Staging L with pre-scaled columns, which takes the multiply off the serial chain, measured 7 % slower: A/B on one box.)
 __device__ __forceinline__ void warp_trsm64(double& v0, double& v1, const double* __restrict__ D, const double* __restrict__ rd, int lane) {
 #pragma unroll 8
   for (int m = 0; m < 32; ++m) {
@@ -386,11 +388,10 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
   double* rd = D + 64 * 65;            // 64
   double* zs = rd + 64;                // 64
   double* P = zs + 64;                 // 64 x 65: panel rows of the next diagonal block (CTA 0)
-  if (blockIdx.x == 0) { chol_diag_tile(bs, 0, 0, false, D, zs, P); chol_diag64(bs, 0, D, rd, zs, flags, nullptr); }
+  if (blockIdx.x == 0) { chol_diag_tile(bs, 0, 0, false, D, zs, P); chol_diag64(bs, 0, D, rd, zs, flags); }
   grid.sync();
   const bool prof = bs.prof != nullptr && blockIdx.x < 2 && tid == 0;
   long long t0 = prof ? gtime_ns() : 0, acc_t[4] = {0, 0, 0, 0}, sub_t[4] = {0, 0, 0, 0};   // sub_t: [0] clock, [1] factor, [2] inverse, [3] tile
-  long long dsub[23] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   auto lap = [&](int slot) { if (prof) { const long long t1 = gtime_ns(); acc_t[slot] += t1 - t0; t0 = t1; } };
   for (int j0 = 0; j0 < bs.n_pad; j0 += NB) {
     const int i_begin = j0 + NB;
@@ -431,7 +432,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
       // critical path: the tile holding the next diagonal block with the whole CTA, then its factorisation
       chol_diag_tile(bs, j0, i_begin, f_next < j0 + NB, D, zs, P);
       if (prof) { const long long t = gtime_ns(); sub_t[3] += t - t0; }
-      chol_diag64(bs, i_begin, D, rd, zs, flags, nullptr);
+      chol_diag64(bs, i_begin, D, rd, zs, flags);
     } else {
       const int group = tid >> 7, gtid = tid & 127;
       double* ring = smem + group * kTileGroupSmem;
