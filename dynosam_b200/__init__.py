@@ -10,3 +10,4 @@ from .api import (  # noqa: F401
     cantor_depair, cantor_pair, default_backend_params, default_lm_params, default_synthetic_config, key_decode, measure_fp64_tflops,
     sliding_window_schedule,
 )
+from . import graphfile  # noqa: E402,F401  (DynoSAM text graph file reader / writer)
