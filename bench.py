@@ -236,6 +236,8 @@ def run_ours(args, rank, world, local_rank):
     clocks = sampler.stop()
     final_error = lm.error()
     tinfo = lm.timing()
+    # accuracy against the synthetic ground truth, outside the timed region
+    accuracy = {"initial": d.metrics.evaluate(scene, g.pose_keys, g.pose_Rt), "final": d.metrics.evaluate(scene, g.pose_keys, lm.values()[0])}
 
     # ---- end-to-end arm: host buffers through the C ABI ----
     e2e_lm = d.GpuLevenbergMarquardt(None, p)
@@ -321,7 +323,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": launches,
         "roofline": roofline, "roofline_all": kernels, "cpu_baseline": cpu_baseline,
         "factor_linearisations_per_s": g.n_factors / (lin_ms * 1e-3),
-        "wall_ms_per_step": wall_ms / args.steps, "final_chi2": final_error,
+        "wall_ms_per_step": wall_ms / args.steps, "final_chi2": final_error, "accuracy": accuracy,
         "phase_ms_per_iteration": {k: phase[k] / max(iters / world, 1) for k in ("linearize_ms", "schur_assemble_ms", "band_cholesky_ms", "band_solve_ms", "evaluate_ms")},
     }
     print(json.dumps(line), flush=True)

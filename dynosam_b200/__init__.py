@@ -11,3 +11,4 @@ from .api import (  # noqa: F401
     sliding_window_schedule,
 )
 from . import graphfile  # noqa: E402,F401  (DynoSAM text graph file reader / writer)
+from . import metrics  # noqa: E402,F401  (ATE / RPE / object-motion error against scene ground truth)
