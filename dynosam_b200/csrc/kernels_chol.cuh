@@ -42,14 +42,14 @@ __device__ __forceinline__ double fast_rsqrt(double d) {
   return y;
 }
 
-// 1/d to double precision (hardware f64 seed + two Newton steps): the only non-FMA operation on the serial chain of the
-// diagonal factorisation below
+// 1/d to double precision: hardware f64 seed y0 (relative error e0 ~ 2^-20 or better), then the cubic step
+// y = y0 (1 + e + e^2), e = 1 - d y0, which leaves e0^3. Three dependent FP64 operations (about 55 cycles each here)
+// instead of the four of two Newton steps: this is the only non-FMA work on the chain of the diagonal factorisation.
 __device__ __forceinline__ double fast_rcp(double d) {
-  double y;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
-  y = y * fma(-d, y, 2.0);
-  y = y * fma(-d, y, 2.0);
-  return y;
+  double y0;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(d));
+  const double e = fma(-d, y0, 1.0);
+  return fma(y0, fma(e, e, e), y0);
 }
 
 // One warp factors the 32 x 32 SPD block A (shared memory, row stride 65, lower triangle) in place, lane = row.
@@ -75,11 +75,11 @@ __device__ __noinline__ void warp_chol32(double* __restrict__ A, int lane, doubl
     for (int c = 0; c < 8; ++c) {
       const double d = __shfl_sync(0xffffffffu, a[c], c0 + c);
       bad |= !(d > 0.0);
-      // trailing update with a[c] / d (one reciprocal on the chain); the column itself is scaled by 1/sqrt(d) off the chain:
-      // a_r[c2] -= L[r][c] L[c2][c] = a_r[c] a_c2[c] / d
-      const double t = a[c] * fast_rcp(d);
+      // trailing update through 1 / d (one reciprocal on the chain); the column itself is scaled by 1/sqrt(d) off the chain
+      // a_r[c2] -= (a_r[c] a_c2[c]) / d : the product does not wait for the reciprocal, one FMA follows it
+      const double inv = fast_rcp(d);
 #pragma unroll
-      for (int c2 = c + 1; c2 < 8; ++c2) a[c2] = fma(-t, __shfl_sync(0xffffffffu, a[c], c0 + c2), a[c2]);
+      for (int c2 = c + 1; c2 < 8; ++c2) a[c2] = fma(-(a[c] * __shfl_sync(0xffffffffu, a[c], c0 + c2)), inv, a[c2]);
       const double rk = fast_rsqrt(d);
       if (lane == c0 + c) rd[c0 + c] = rk;
       a[c] *= rk;   // L[lane][c0 + c] (diagonal: d * rsqrt(d) = sqrt(d))
@@ -282,22 +282,26 @@ __global__ void __launch_bounds__(256) k_band_diag_inverse(BandSystem bs) {
   for (int idx = tid; idx < 64 * 64; idx += 256) out[idx] = Li[(idx >> 6) * 65 + (idx & 63)];
 }
 
-// element k (k = lane, lane + 32) of a 64-vector held as v0/v1 across a warp:  v <- v L^-T  (rows: x L^T = a),
-// L (64 x 64 lower, row stride 65) and the reciprocals of its diagonal in shared memory.
-// (Staging L with pre-scaled columns, which takes the multiply off the serial chain, measured 7 % slower: A/B on one box.)
-__device__ __forceinline__ void warp_trsm64(double& v0, double& v1, const double* __restrict__ D, const double* __restrict__ rd, int lane) {
+// element k (k = lane, lane + 32) of a 64-vector held as v0/v1 across a warp:  v <- v L^-T  (rows: x L^T = a).
+// Ds = L with column m scaled by rd[m] = 1 / L_mm (64 x 64 lower, row stride 65, shared memory). With u_m the running
+// residual entry, x_m = u_m rd[m] and every later entry loses u_m Ds[j][m]: the serial chain per column is one shuffle
+// and one FMA (a dependent FP64 operation costs about 55 cycles on this part, so the multiply by rd[m] is kept off the
+// chain, and written as straight-line selects: a divergent branch around it serialises the two sides).
+__device__ __forceinline__ void warp_trsm64(double& v0, double& v1, const double* __restrict__ Ds, const double* __restrict__ rd, int lane) {
 #pragma unroll 8
   for (int m = 0; m < 32; ++m) {
-    const double xm = __shfl_sync(0xffffffffu, v0, m) * rd[m];
-    if (lane == m) v0 = xm;
-    else if (lane > m) v0 = fma(-xm, D[lane * 65 + m], v0);
-    v1 = fma(-xm, D[(lane + 32) * 65 + m], v1);
+    const double um = __shfl_sync(0xffffffffu, v0, m);
+    const double xs = um * rd[m];
+    const double upd = fma(-um, Ds[lane * 65 + m], v0);
+    v0 = lane == m ? xs : (lane > m ? upd : v0);
+    v1 = fma(-um, Ds[(lane + 32) * 65 + m], v1);
   }
 #pragma unroll 8
   for (int m = 32; m < 64; ++m) {
-    const double xm = __shfl_sync(0xffffffffu, v1, m - 32) * rd[m];
-    if (lane == m - 32) v1 = xm;
-    else if (lane > m - 32) v1 = fma(-xm, D[(lane + 32) * 65 + m], v1);
+    const double um = __shfl_sync(0xffffffffu, v1, m - 32);
+    const double xs = um * rd[m];
+    const double upd = fma(-um, Ds[(lane + 32) * 65 + m], v1);
+    v1 = lane == m - 32 ? xs : (lane > m - 32 ? upd : v1);
   }
 }
 
@@ -403,9 +407,9 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
     const int i_first = i_begin + gwarp;
     double p0 = 0.0, p1 = 0.0;
     if (i_first < i_end) { const double* rp = S + (size_t)i_first * ld + (j0 - i_first + bw); p0 = rp[lane]; p1 = rp[lane + 32]; }
-    for (int idx = tid; idx < 64 * 64; idx += kCholThreads) {
+    for (int idx = tid; idx < 64 * 64; idx += kCholThreads) {   // L_JJ with its columns scaled by the reciprocal diagonal
       const int r = idx >> 6, c = idx & 63;
-      D[r * 65 + c] = (c <= r) ? S[(size_t)(j0 + r) * ld + (c - r + bw)] : 0.0;
+      D[r * 65 + c] = (c <= r) ? S[(size_t)(j0 + r) * ld + (c - r + bw)] * bs.rdiag[j0 + c] : 0.0;
     }
     if (tid < 64) { zs[tid] = bs.z[j0 + tid]; rd[tid] = bs.rdiag[j0 + tid]; }
     __syncthreads();
@@ -415,7 +419,9 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
       double v0, v1;
       if (i == i_first) { v0 = p0; v1 = p1; } else { v0 = rowp[lane]; v1 = rowp[lane + 32]; }
       if (__all_sync(0xffffffffu, v0 == 0.0 && v1 == 0.0)) continue;   // outside the envelope: nothing to solve, nothing to carry
+      if (prof) { const long long t = gtime_ns(); sub_t[2] += t - t0; }
       warp_trsm64(v0, v1, D, rd, lane);
+      if (prof) { const long long t = gtime_ns(); sub_t[3] += t - t0; }
       rowp[lane] = v0; rowp[lane + 32] = v1;
       const double dot = warp_sum(v0 * zs[lane] + v1 * zs[lane + 32]);
       if (lane == 0) bs.y[i] -= dot;
@@ -436,7 +442,9 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
     } else {
       const int group = tid >> 7, gtid = tid & 127;
       double* ring = smem + group * kTileGroupSmem;
-      for (int id = 1 + (blockIdx.x - 1) * 4 + group; id < ntile; id += (gridDim.x - 1) * 4) {
+      // tile ids are dealt round-robin over the CTAs (group g of CTA b takes b - 1 + g (G - 1), ...): a CTA's four tiles come
+      // from different parts of the window, so envelope skipping does not leave whole CTAs idle next to fully loaded ones
+      for (int id = 1 + (int)(blockIdx.x - 1) + group * (int)(gridDim.x - 1); id < ntile; id += (gridDim.x - 1) * 4) {
         int ti = (int)((sqrtf(8.0f * id + 1.0f) - 1.0f) * 0.5f);
         while ((ti + 1) * (ti + 2) / 2 <= id) ++ti;
         while (ti * (ti + 1) / 2 > id) --ti;
@@ -454,7 +462,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
   }
   if (prof) for (int k = 0; k < 4; ++k) bs.prof[4 * blockIdx.x + k] = acc_t[k];
   if (prof && blockIdx.x == 0) bs.prof[8] = sub_t[3];
-  if (prof && blockIdx.x == 1) { bs.prof[9] = sub_t[0]; bs.prof[10] = sub_t[1]; }
+  if (prof && blockIdx.x == 1) { bs.prof[9] = sub_t[0]; bs.prof[10] = sub_t[1]; bs.prof[11] = sub_t[2]; bs.prof[12] = sub_t[3]; }
 }
 
 // Backward substitution x = L^-T z after k_band_cholesky (which left z = L^-1 rhs and the inverses of the
