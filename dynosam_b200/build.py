@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(LIB_DIR, "libdynosam_b200.so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-Xcompiler", "-fopenmp", "-shared", "--cudart", "shared", "-lgomp",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-fopenmp", "-shared", "--cudart", "shared", "-lgomp", "-ldl",
 ]
 
 
