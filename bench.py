@@ -367,6 +367,8 @@ def run_ours(args, rank, world, local_rank):
         "config": {"workload": WORKLOAD_NAMES[args.workload], "formulation": "MotionInWorld (world-centric; the fork has no hybrid formulation)",
                    "lm_iterations_per_step": LM_ITERS, "factors": g.n_factors, "measurements": g.n_p2p, "poses": g.n_pose, "points": g.n_point,
                    "reduced_dim": int(tinfo["reduced_dim"]), "half_bandwidth": int(tinfo["half_bandwidth"]),
+                   "band_fronts": tinfo["band_fronts"], "band_split": tinfo["band_split"], "band_separator": tinfo["band_separator"],
+                   "band_single_front_repeats": tinfo["band_single_front_repeats"],
                    "l2": "inputs larger than L2 (band %d MiB + graph and caches), no flush" % (int(tinfo["band_bytes"]) >> 20),
                    "parallelism": "1 GPU" if world == 1 else
                    ("one scene sharded by object and landmark over %d GPUs; NCCL all-reduce of the reduced system, gradient and error sums; every rank factors the band" % world

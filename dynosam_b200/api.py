@@ -376,7 +376,9 @@ class GpuLevenbergMarquardt:
         names = ["optimize_ms", "linearize_ms", "assemble_ms", "solve_ms", "evaluate_ms", "h2d_ms", "d2h_ms", "n_linearize",
                  "pcg_iterations", "kernel_launches", "n_error_passes", "n_solves", "schur_assemble_ms", "band_cholesky_ms", "band_solve_ms", "band_flops", "envelope_blocks", "h2d_bytes", "band_bytes",
                  "half_bandwidth", "reduced_dim"]
-        return dict(zip(names, t.tolist()))
+        out = dict(zip(names, t.tolist()))
+        out.update(band_fronts=int(t[28]), band_split=int(t[29]), band_separator=int(t[30]), band_single_front_repeats=int(t[31]))
+        return out
 
     def hessian_pattern(self):
         n, nnz = C.c_int64(), C.c_int64()

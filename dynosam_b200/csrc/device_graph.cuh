@@ -116,7 +116,31 @@ struct BandSystem {
   double* Linv = nullptr;          // [n_pad / 64][64 x 64] inverses of the diagonal blocks of the factor
   long long* prof = nullptr;       // optional [8] ns counters of the factorisation phases (verbose >= 3)
   const int* first64 = nullptr;    // [n_pad / 64] smallest first envelope column over each group of 64 rows
+  // Two-front (twisted) factorisation: a front is a band storage over a contiguous range of the time-ordered system that
+  // is eliminated towards the separator in the middle. n stays the real dimension of the whole system, n_pad is the
+  // number of rows of THIS storage.
+  int rev = 0;                     // local row i holds global row n_glob - 1 - i (the front that eliminates backwards in time)
+  int n_glob = 0;                  // padded dimension of the whole system
+  int j_begin = 0, n_elim = 0;     // a k_band_cholesky launch eliminates the columns [j_begin, n_elim) of this storage
+  int n_known = 0;                 // trailing rows whose solution is given in xt (the separator, solved on the other front)
+  int g_lo = 0, g_hi = 0;          // global rows whose right-hand side this front carries (others start at zero)
+  double* xt = nullptr;            // [n_glob] solution in time order, shared by the fronts
 };
+
+// Where element (i, j), i >= j, of the time-ordered reduced system lives: the forward storage for the columns left of
+// the split m and for the separator block [m, ms) x [m, ms), the backward storage (rows and columns reversed, which
+// turns the upper triangle of the trailing part into a lower band again) for everything below the separator.
+// One front: m = ms = N, everything is in SF.
+struct BandMap {
+  double* SF = nullptr;
+  double* SB = nullptr;
+  int ld = 0, bw = 0, m = 0, ms = 0, N = 0;
+};
+__device__ __forceinline__ double* band_at(const BandMap& bm, int i, int j) {
+  if (j < bm.m || i < bm.ms) return bm.SF + (size_t)i * bm.ld + (j + bm.bw - i);
+  const int r = bm.N - 1 - j, c = bm.N - 1 - i;
+  return bm.SB + (size_t)r * bm.ld + (c + bm.bw - r);
+}
 
 enum Scal : int {
   kErr = 0,        // nonlinear error of the evaluated state

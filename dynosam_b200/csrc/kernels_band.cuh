@@ -70,6 +70,10 @@ __global__ void __launch_bounds__(256) k_fp64_peak(double* out, int iters) {
 __global__ void k_band_pad_identity(BandSystem bs) {
   for (int i = bs.n + threadIdx.x; i < bs.n_pad; i += blockDim.x) bs.S[(size_t)i * bs.ld + bs.bw] = 1.0;
 }
+// the same for the backward front, where the padding rows of the system come first: local rows [0, count)
+__global__ void k_band_pad_identity_front(BandSystem bs, int count) {
+  for (int i = threadIdx.x; i < count; i += blockDim.x) bs.S[(size_t)i * bs.ld + bs.bw] = 1.0;
+}
 
 // scal[dst] = sum v[i]^2 (single block)
 __global__ void __launch_bounds__(1024) k_norm2(int n, const double* __restrict__ v, double* __restrict__ scal, int dst) {

@@ -411,12 +411,21 @@ __device__ __forceinline__ void chol_update_tile(const BandSystem& bs, int j0, i
   }
 }
 
-__global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs, int* __restrict__ flags) {
+// One launch eliminates the columns [j_begin, n_elim) of one storage (nfront = 1), or of two independent storages side by
+// side (nfront = 2: the two fronts of the twisted factorisation, half of the grid each, sharing the grid barriers). The
+// factorisation is bound by the serial chain of its panels, not by arithmetic, so two chains of half the length on one
+// device take about half the time. `iters` = the larger panel count of the fronts (the host knows it).
+__global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs0, BandSystem bs1, int nfront, int iters, int* __restrict__ flags) {
   cg::grid_group grid = cg::this_grid();
   extern __shared__ double smem[];
   constexpr int NB = kBandNB;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int gwarp = blockIdx.x * (kCholThreads / 32) + wid, nwarp = gridDim.x * (kCholThreads / 32);
+  const int per = gridDim.x / nfront;                       // CTAs per front
+  const int front = blockIdx.x / per;
+  const bool idle = front >= nfront;                        // left-over CTAs of an odd grid only keep the barriers company
+  const BandSystem bs = (front == 1) ? bs1 : bs0;
+  const int lb = blockIdx.x - front * per;                  // CTA index within the front
+  const int gwarp = lb * (kCholThreads / 32) + wid, nwarp = per * (kCholThreads / 32);
   const size_t ld = bs.ld;
   const int bw = bs.bw;
   double* __restrict__ S = bs.S;
@@ -424,17 +433,20 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
   double* rd = D + 64 * 65;            // 64
   double* zs = rd + 64;                // 64
   double* P = zs + 64;                 // 64 x 65: panel rows of the next diagonal block (CTA 0)
-  if (blockIdx.x == 0) { chol_diag_tile(bs, 0, 0, false, D, zs, P); chol_diag64(bs, 0, D, rd, zs, flags); }
+  if (lb == 0 && !idle && bs.j_begin < bs.n_elim) { chol_diag_tile(bs, 0, bs.j_begin, false, D, zs, P); chol_diag64(bs, bs.j_begin, D, rd, zs, flags); }
   grid.sync();
-  const bool prof = bs.prof != nullptr && blockIdx.x < 2 && tid == 0;
+  const bool prof = bs.prof != nullptr && nfront == 1 && blockIdx.x < 2 && tid == 0;
   long long t0 = prof ? gtime_ns() : 0, acc_t[4] = {0, 0, 0, 0}, sub_t[4] = {0, 0, 0, 0};   // sub_t: [0] clock, [1] factor, [2] inverse, [3] tile
   auto lap = [&](int slot) { if (prof) { const long long t1 = gtime_ns(); acc_t[slot] += t1 - t0; t0 = t1; } };
-  for (int j0 = 0; j0 < bs.n_pad; j0 += NB) {
+  for (int it = 0; it < iters; ++it) {
+    const int j0 = bs.j_begin + it * NB;
     const int i_begin = j0 + NB;
     const int i_end = min(bs.n_pad, i_begin + bs.window);
-    if (i_begin >= bs.n_pad) break;
+    const bool act = !idle && j0 < bs.n_elim && i_begin < bs.n_pad;   // this front still has a panel with rows below it
+    int f_next = 0;
+    if (act) {
     // ---- phase A: L_iJ = A_iJ L_JJ^-T for the rows below the panel (substitution, one warp per row), rhs carried along ----
-    const int f_next = bs.first64[i_begin >> 6];   // envelope start of the next diagonal block's rows (used in phase B)
+    f_next = bs.first64[i_begin >> 6];   // envelope start of the next diagonal block's rows (used in phase B)
     // the first row of this warp is requested before L_JJ is staged: the two L2 round trips overlap
     const int i_first = i_begin + gwarp;
     double p0 = 0.0, p1 = 0.0;
@@ -460,23 +472,29 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
     }
     if (prof) { const long long t = gtime_ns(); sub_t[1] += t - t0; }
     __syncthreads();
+    }
     lap(0);
     grid.sync();
     lap(1);
+    if (act) {
     // ---- phase B: trailing update of the window in 64 x 64 tiles (ti, tj), tj <= ti ----
     const int nt = (i_end - i_begin + 63) / 64;
     const int ntile = nt * (nt + 1) / 2;
-    if (blockIdx.x == 0) {
+    const bool factor_next = i_begin < bs.n_elim;   // false after the last panel of a front: its trailing block waits for the other front
+    if (lb == 0 && factor_next) {
       // critical path: the tile holding the next diagonal block with the whole CTA, then its factorisation
       chol_diag_tile(bs, j0, i_begin, f_next < j0 + NB, D, zs, P);
       if (prof) { const long long t = gtime_ns(); sub_t[3] += t - t0; }
       chol_diag64(bs, i_begin, D, rd, zs, flags);
+    } else if (lb == 0) {
+      // the first diagonal block of the trailing matrix is an ordinary tile now
+      if (tid < 128 && f_next < j0 + NB) chol_update_tile(bs, j0, i_begin, i_begin, i_end, smem, tid, 0);
     } else {
       const int group = tid >> 7, gtid = tid & 127;
       double* ring = smem + group * kTileGroupSmem;
       // tile ids are dealt round-robin over the CTAs (group g of CTA b takes b - 1 + g (G - 1), ...): a CTA's four tiles come
       // from different parts of the window, so envelope skipping does not leave whole CTAs idle next to fully loaded ones
-      for (int id = 1 + (int)(blockIdx.x - 1) + group * (int)(gridDim.x - 1); id < ntile; id += (gridDim.x - 1) * 4) {
+      for (int id = 1 + (lb - 1) + group * (per - 1); id < ntile; id += (per - 1) * 4) {
         int ti = (int)((sqrtf(8.0f * id + 1.0f) - 1.0f) * 0.5f);
         while ((ti + 1) * (ti + 2) / 2 <= id) ++ti;
         while (ti * (ti + 1) / 2 > id) --ti;
@@ -488,6 +506,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
       }
     }
     __syncthreads();
+    }
     lap(2);
     grid.sync();
     lap(3);
@@ -495,6 +514,22 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
   if (prof) for (int k = 0; k < 4; ++k) bs.prof[4 * blockIdx.x + k] = acc_t[k];
   if (prof && blockIdx.x == 0) bs.prof[8] = sub_t[3];
   if (prof && blockIdx.x == 1) { bs.prof[9] = sub_t[0]; bs.prof[10] = sub_t[1]; bs.prof[11] = sub_t[2]; bs.prof[12] = sub_t[3]; }
+}
+
+// Two-front factorisation, between the fronts and the separator: the backward front's trailing block (its Schur
+// complement on the separator, in reversed order) and the right-hand side it carried are added to the forward
+// storage, which then holds the complete separator system S_sep = A_sep - C_0 A_0^-1 C_0^T - C_1 A_1^-1 C_1^T.
+// m = first separator row in the forward storage, s = separator size.
+__global__ void __launch_bounds__(256) k_band_combine(BandSystem F, BandSystem B, int m, int s) {
+  const int a = blockIdx.x;   // separator row
+  const int nB = B.n_pad;
+  for (int b = threadIdx.x; b <= a; b += blockDim.x) {
+    if (a - b > F.bw) continue;
+    const size_t rF = (size_t)(m + a);
+    const size_t rB = (size_t)(nB - 1 - b);
+    F.S[rF * F.ld + ((m + b) + F.bw - (m + a))] += B.S[rB * B.ld + ((nB - 1 - a) + B.bw - (nB - 1 - b))];
+  }
+  if (threadIdx.x == 0) F.y[m + a] += B.y[nB - 1 - a];
 }
 
 // Backward substitution x = L^-T z after k_band_cholesky (which left z = L^-1 rhs and the inverses of the
@@ -525,8 +560,10 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
   double lc[64], li[16];
   auto prefetch = [&](int j0, int c) {
     const double* Li = bs.Linv + (size_t)(j0 >> 6) * 4096;
+    if (j0 < bs.n_pad - bs.n_known) {
 #pragma unroll
-    for (int mm = 0; mm < 16; ++mm) li[mm] = Li[(pt * 16 + mm) * 64 + k];   // Linv is zero above the diagonal
+      for (int mm = 0; mm < 16; ++mm) li[mm] = Li[(pt * 16 + mm) * 64 + k];   // Linv is zero above the diagonal
+    }
     if (c >= 0) {
       const double* col = S + (size_t)j0 * ld + (c - j0 + bw);   // element (j0 + rr, c) at col[rr * (ld - 1)]
 #pragma unroll
@@ -538,21 +575,29 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
   double zreg = c >= 0 ? z[c] : 0.0;
   prefetch(j0, c);
   for (; j0 >= 0; j0 -= 64) {
+    const bool known = j0 >= bs.n_pad - bs.n_known;   // separator rows of the backward front: solved on the forward front
     {  // x_k = sum_{m >= k} Linv[m][k] z_m
       double s = 0.0;
+      if (!known) {
 #pragma unroll
-      for (int mm = 0; mm < 16; ++mm) s = fma(li[mm], z[j0 + pt * 16 + mm], s);
+        for (int mm = 0; mm < 16; ++mm) s = fma(li[mm], z[j0 + pt * 16 + mm], s);
+      }
       part[pt][k] = s;
     }
     __syncthreads();
     if (tid < 64) {
-      const double v = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
-      xs[tid] = v;
       const int i = j0 + tid;
-      if (blockIdx.x == 0 && i < bs.n) {
-        const int p = i / 6, cc = i - 6 * p;
-        double* dst = x + 6 * (size_t)bs.pos_pose[p] + cc;
-        *dst = add_to_x ? *dst + v : v;
+      const int gi = bs.rev ? bs.n_glob - 1 - i : i;   // row of the time-ordered system
+      double v = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
+      if (known) v = bs.xt[gi];
+      xs[tid] = v;
+      if (blockIdx.x == 0 && !known) {
+        if (bs.xt) bs.xt[gi] = v;
+        if (gi < bs.n) {
+          const int p = gi / 6, cc = gi - 6 * p;
+          double* dst = x + 6 * (size_t)bs.pos_pose[p] + cc;
+          *dst = add_to_x ? *dst + v : v;
+        }
       }
     }
     __syncthreads();
@@ -650,12 +695,14 @@ __global__ void __launch_bounds__(kBackThreads) k_band_fwdsolve(BandSystem bs) {
   }
 }
 
-// y[time order] = b[natural pose order]; zero on the padding
+// y[time order] = b[natural pose order] for the rows this storage carries (all of them for a single front); zero on the
+// padding and on the rows another front carries
 __global__ void __launch_bounds__(256) k_band_load_rhs(BandSystem bs, const double* __restrict__ b) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= bs.n_pad) return;
+  const int gi = bs.rev ? bs.n_glob - 1 - i : i;
   double v = 0.0;
-  if (i < bs.n) { const int p = i / 6, c = i - 6 * p; v = b[6 * (size_t)bs.pos_pose[p] + c]; }
+  if (gi < bs.n && gi >= bs.g_lo && gi < bs.g_hi) { const int p = gi / 6, c = gi - 6 * p; v = b[6 * (size_t)bs.pos_pose[p] + c]; }
   bs.y[i] = v;
 }
 

@@ -28,6 +28,7 @@ def main():
         p = d.default_lm_params()
         p.device = local
         p.max_iterations = 6
+        p.linear_solver = 4 if name == "medium" else 3   # the sharded exchange with the two-front and with the single-front factorisation
         uid = [sharded.make_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         lm = sharded.ShardedLevenbergMarquardt(g, rank, world, uid[0], p)
@@ -53,6 +54,7 @@ def main():
                 "trace_rel": float(np.max(np.abs(tr - rtr) / np.maximum(np.abs(rtr), 1e-12))) if len(tr) == len(rtr) else None,
                 "pose": float(np.abs(pose - r_pose).max()), "points": float(np.abs(merged - r_pts).max()),
                 "collectives": t["collectives"], "collective_bytes": t["collective_bytes"], "band_allreduce_ms": t["band_allreduce_ms"],
+                "band_fronts": t["band_fronts"], "single_front_repeats": t["band_single_front_repeats"],
             }
         del lm
         dist.barrier()

@@ -220,3 +220,33 @@ def test_baseline_config2_size_matches_oracle():
     assert gpu.iterations() == r["iterations"] and gpu.getInnerIterations() == r["inner_iterations"]
     tr_g, tr_c = np.array(gpu.error_trace), np.array(r["error_trace"])
     assert np.all(np.abs(tr_g - tr_c) <= CHI2_RTOL * np.abs(tr_c)), (tr_g, tr_c)
+
+
+# ---- two-front (twisted) band factorisation against the single front ----
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene_name", ["small", "medium", "long"])
+def test_two_front_factorisation_matches_single_front(scene_name):
+    scene = {"small": lambda: scenes.small_noisy(), "medium": lambda: scenes.medium_noisy(),
+             "long": lambda: d.Scene.synthetic(n_frames=400, n_objects=6, static_per_frame=40, dynamic_per_object=10, object_span=120,
+                                               static_track_max=12, dynamic_track_max=10, seed=21)}[scene_name]()
+    g = scene.full_batch_graph()
+    res = {}
+    for solver in (3, 4):
+        p = d.default_lm_params()
+        p.linear_solver = solver
+        p.max_iterations = 6
+        lm = d.GpuLevenbergMarquardt(g, p)
+        ok, dp, dpt, _ = lm.solve_once(1e-4)
+        pose, pts = lm.optimize()
+        res[solver] = (ok, dp, dpt, pose, pts, list(lm.error_trace), lm.iterations(), lm.getInnerIterations(), lm.timing())
+    assert res[4][8]["band_single_front_repeats"] == 0                  # the two-front solves met the residual tolerance themselves
+    assert res[3][8]["band_fronts"] == 1
+    assert res[4][8]["band_fronts"] == 2, "scene too short for two fronts: %r" % (res[4][8],)
+    assert res[3][0] and res[4][0]
+    scale = max(np.abs(res[3][1]).max(), 1e-300)
+    assert np.abs(res[4][1] - res[3][1]).max() / scale < 1e-8          # one damped solve, pose step
+    assert np.abs(res[4][2] - res[3][2]).max() / max(np.abs(res[3][2]).max(), 1e-300) < 1e-8
+    assert res[4][6:8] == res[3][6:8]                                   # same LM counters
+    np.testing.assert_allclose(res[4][5], res[3][5], rtol=1e-9)         # same chi2 trace
+    np.testing.assert_allclose(res[4][3], res[3][3], atol=1e-7)
+    np.testing.assert_allclose(res[4][4], res[3][4], atol=1e-7)

@@ -61,3 +61,4 @@ def test_two_ranks_match_single_gpu():
         assert r["trace_rel"] is not None and r["trace_rel"] < 1e-6, (name, r)   # north_star: final chi2 within 1e-6 relative
         assert r["pose"] < 1e-6 and r["points"] < 1e-6, (name, r)
         assert r["collectives"] > 0
+        assert r["band_fronts"] == (2 if name == "medium" else 1) and r["single_front_repeats"] == 0, (name, r)
