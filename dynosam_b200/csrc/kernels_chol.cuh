@@ -538,16 +538,24 @@ __global__ void __launch_bounds__(256) k_band_combine(BandSystem F, BandSystem B
 // the z entries of the window columns left of the panel, one column per thread (row-panel reads are contiguous).
 // x is written in natural pose order. z is consumed.
 constexpr int kBackThreads = 256;
-__global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, double* __restrict__ x, int add_to_x) {
+// A launch walks the panels [j_begin, n_elim) of a storage from the top down; with nfront = 2 two storages side by side on
+// half of the grid each (the two fronts of the twisted factorisation, once the separator is solved), `iters` = the larger
+// panel count. z entries still held in registers are published at the end, so a later launch can continue below j_begin.
+__global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs0, BandSystem bs1, int nfront, int iters, double* __restrict__ x, int add_to_x) {
   cg::grid_group grid = cg::this_grid();
   __shared__ double part[4][64];
   __shared__ double xs[64];
   const int tid = threadIdx.x;
+  const int per = gridDim.x / nfront;
+  const int front = blockIdx.x / per;
+  const bool idle = front >= nfront;
+  const BandSystem bs = (front == 1) ? bs1 : bs0;
+  const int lb = blockIdx.x - front * per;
   const size_t ld = bs.ld;
   const int bw = bs.bw;
   const double* __restrict__ S = bs.S;
   double* __restrict__ z = bs.z;
-  const int gtid = blockIdx.x * kBackThreads + tid, gsize = gridDim.x * kBackThreads;   // gsize >= window + 64
+  const int gtid = lb * kBackThreads + tid, gsize = per * kBackThreads;   // gsize >= window + 64
   // a thread owns the columns congruent to gtid modulo gsize: at most one of them lies in the window of a panel, and
   // it stays the same from panel to panel until the panels reach it, so its z entry lives in a register meanwhile
   auto column_of = [&](int j0) {
@@ -570,11 +578,17 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
       for (int rr = 0; rr < 64; ++rr) lc[rr] = (j0 + rr - c <= bw) ? col[(size_t)rr * (ld - 1)] : 0.0;
     }
   };
-  int j0 = bs.n_pad - 64;
-  int c = column_of(j0);
-  double zreg = c >= 0 ? z[c] : 0.0;
-  prefetch(j0, c);
-  for (; j0 >= 0; j0 -= 64) {
+  int j0 = bs.n_elim - 64;
+  int c = -1;
+  double zreg = 0.0;
+  if (!idle && j0 >= bs.j_begin) {
+    c = column_of(j0);
+    zreg = c >= 0 ? z[c] : 0.0;
+    prefetch(j0, c);
+  }
+  for (int it = 0; it < iters; ++it, j0 -= 64) {
+    const bool act = !idle && j0 >= bs.j_begin;
+    if (act) {
     const bool known = j0 >= bs.n_pad - bs.n_known;   // separator rows of the backward front: solved on the forward front
     {  // x_k = sum_{m >= k} Linv[m][k] z_m
       double s = 0.0;
@@ -591,7 +605,7 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
       double v = part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid];
       if (known) v = bs.xt[gi];
       xs[tid] = v;
-      if (blockIdx.x == 0 && !known) {
+      if (lb == 0 && !known) {
         if (bs.xt) bs.xt[gi] = v;
         if (gi < bs.n) {
           const int p = gi / 6, cc = gi - 6 * p;
@@ -608,7 +622,7 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
       zreg -= s;
     }
     const int j1 = j0 - 64;
-    if (j1 >= 0) {
+    if (j1 >= bs.j_begin) {
       const int c1 = column_of(j1);
       if (c1 != c) {
         if (c >= 0) z[c] = zreg;              // c joins the next panel: publish before the barrier
@@ -616,6 +630,10 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs, 
         c = c1;
       }
       prefetch(j1, c);                          // in flight across the barrier
+    } else if (c >= 0) {
+      z[c] = zreg;                              // last panel of this launch: hand the partial sums to whoever continues below
+      c = -1;
+    }
     }
     grid.sync();
   }
