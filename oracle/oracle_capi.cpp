@@ -5,6 +5,7 @@
 #include <cstdint>
 #include <cstring>
 
+#include "llworld.hpp"
 #include "lm.hpp"
 
 using namespace oracle;
@@ -158,6 +159,46 @@ void oracle_ternary_error(const double* mp, const double* mc, const double* H, d
   Vec3 e = motion_ternary_error({mp[0], mp[1], mp[2]}, {mc[0], mc[1], mc[2]}, pose_from(H), J1, J2, J3);
   e3[0] = e.x; e3[1] = e.y; e3[2] = e.z;
 }
+// LLWorld factors, batched: whitened + robust-reweighted blocks and b = -whitened residual (NoiseModelFactor::linearize),
+// *error = sum of the robust losses
+void oracle_llworld_motion_pose(int64_t n, const double* prev_point, const double* cur_point, const double* prev_pose, const double* cur_pose, double sigma, double huber_k,
+                                double* A_prev_point, double* A_cur_point, double* A_prev_pose, double* A_cur_pose, double* b, double* error) {
+  double total = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    double J1[9], J2[9], J3[18], J4[18];
+    const Vec3 mp = {prev_point[3 * i], prev_point[3 * i + 1], prev_point[3 * i + 2]}, mc = {cur_point[3 * i], cur_point[3 * i + 1], cur_point[3 * i + 2]};
+    const Vec3 e = landmark_motion_pose_error(mp, mc, pose_from(prev_pose + 12 * i), pose_from(cur_pose + 12 * i), J1, J2, J3, J4);
+    const double dist = norm(e) / sigma;
+    total += robust_loss(dist, huber_k);
+    const double sw = robust_sqrt_weight(dist, huber_k) / sigma;
+    for (int k = 0; k < 9; ++k) { if (A_prev_point) A_prev_point[9 * i + k] = sw * J1[k]; if (A_cur_point) A_cur_point[9 * i + k] = sw * J2[k]; }
+    for (int k = 0; k < 18; ++k) { if (A_prev_pose) A_prev_pose[18 * i + k] = sw * J3[k]; if (A_cur_pose) A_cur_pose[18 * i + k] = sw * J4[k]; }
+    if (b) { b[3 * i] = -sw * e.x; b[3 * i + 1] = -sw * e.y; b[3 * i + 2] = -sw * e.z; }
+  }
+  if (error) *error = total;
+}
+void oracle_llworld_pose_smoothing(int64_t n, const double* pose_k2, const double* pose_k1, const double* pose_k, const double* sigmas6,
+                                   double* A_k2, double* A_k1, double* A_k, double* b, double* error) {
+  double total = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    double e[6], J1[36], J2[36], J3[36];
+    landmark_pose_smoothing_error(pose_from(pose_k2 + 12 * i), pose_from(pose_k1 + 12 * i), pose_from(pose_k + 12 * i), e, J1, J2, J3);
+    double d2 = 0;
+    for (int r = 0; r < 6; ++r) { const double w = e[r] / sigmas6[r]; d2 += w * w; }
+    total += 0.5 * d2;
+    for (int r = 0; r < 6; ++r) {
+      const double is = 1.0 / sigmas6[r];
+      for (int c = 0; c < 6; ++c) {
+        if (A_k2) A_k2[36 * i + 6 * r + c] = is * J1[6 * r + c];
+        if (A_k1) A_k1[36 * i + 6 * r + c] = is * J2[6 * r + c];
+        if (A_k) A_k[36 * i + 6 * r + c] = is * J3[6 * r + c];
+      }
+      if (b) b[6 * i + r] = -is * e[r];
+    }
+  }
+  if (error) *error = total;
+}
+
 double oracle_robust_loss(double dist, double k) { return robust_loss(dist, k); }
 double oracle_robust_sqrt_weight(double dist, double k) { return robust_sqrt_weight(dist, k); }
 

@@ -52,6 +52,8 @@ def lib():
                         ("oracle_se3_inverse", 2), ("oracle_se3_retract", 3), ("oracle_between_error", 6), ("oracle_prior_error", 4),
                         ("oracle_p2p_error", 6), ("oracle_ternary_error", 7)]:
             getattr(_lib, name).argtypes = [_dp] * n
+        _lib.oracle_llworld_motion_pose.argtypes = [C.c_int64] + [_dp] * 4 + [C.c_double, C.c_double] + [_dp] * 6
+        _lib.oracle_llworld_pose_smoothing.argtypes = [C.c_int64] + [_dp] * 4 + [_dp] * 5
         _lib.oracle_robust_loss.restype = C.c_double
         _lib.oracle_robust_loss.argtypes = [C.c_double, C.c_double]
         _lib.oracle_robust_sqrt_weight.restype = C.c_double
@@ -179,3 +181,29 @@ class OracleGraph:
         if getattr(self, "_h", None):
             lib().oracle_graph_destroy(self._h)
             self._h = None
+
+
+def _c(a):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return a, a.ctypes.data_as(_dp)
+
+
+def llworld_motion_pose(prev_point, cur_point, prev_pose, cur_pose, sigma, huber_k=0.0):
+    """Oracle restatement of LandmarkMotionPoseFactor linearised (central-difference Jacobians), batched."""
+    (pp, a1), (cp, a2), (pl, a3), (cl, a4) = _c(prev_point), _c(cur_point), _c(prev_pose), _c(cur_pose)
+    n = len(pp)
+    out = {"A_prev_point": np.zeros((n, 3, 3)), "A_cur_point": np.zeros((n, 3, 3)), "A_prev_pose": np.zeros((n, 3, 6)), "A_cur_pose": np.zeros((n, 3, 6)), "b": np.zeros((n, 3))}
+    err = C.c_double()
+    lib().oracle_llworld_motion_pose(n, a1, a2, a3, a4, sigma, huber_k, *[v.ctypes.data_as(_dp) for v in out.values()], C.cast(C.byref(err), _dp))
+    out["error"] = err.value
+    return out
+
+
+def llworld_pose_smoothing(pose_k2, pose_k1, pose_k, sigmas):
+    (p2, a1), (p1, a2), (p0, a3), (sg, a4) = _c(pose_k2), _c(pose_k1), _c(pose_k), _c(sigmas)
+    n = len(p2)
+    out = {"A_k2": np.zeros((n, 6, 6)), "A_k1": np.zeros((n, 6, 6)), "A_k": np.zeros((n, 6, 6)), "b": np.zeros((n, 6))}
+    err = C.c_double()
+    lib().oracle_llworld_pose_smoothing(n, a1, a2, a3, a4, *[v.ctypes.data_as(_dp) for v in out.values()], C.cast(C.byref(err), _dp))
+    out["error"] = err.value
+    return out
