@@ -224,7 +224,10 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         quiet_nccl()
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        with stdout_to_stderr():     # NCCL prints its version banner on stdout when the first communicator is made
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
     sharded_mode = bool(args.sharded) and world > 1
     p = lm_params(local_rank)
     if sharded_mode:
@@ -405,7 +408,10 @@ def run_windows(args, rank, world, local_rank):
     if world > 1:
         quiet_nccl()
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        with stdout_to_stderr():     # NCCL prints its version banner on stdout when the first communicator is made
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            dist.barrier()
+            torch.cuda.synchronize()
     scene = d.Scene.synthetic(**WORKLOADS["cfg3"])
     sched = d.sliding_window_schedule(WINDOW, OVERLAP, 0, WORKLOADS["cfg3"]["n_frames"] - 1)[:N_WINDOWS]
     mine = sched[rank::world]            # windows are independent solves: sharded over ranks, no data-path collective
