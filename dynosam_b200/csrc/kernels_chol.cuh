@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
   double* P = zs + 64;                 // 64 x 65: panel rows of the next diagonal block (CTA 0)
   if (lb == 0 && !idle && bs.j_begin < bs.n_elim) { chol_diag_tile(bs, 0, bs.j_begin, false, D, zs, P); chol_diag64(bs, bs.j_begin, D, rd, zs, flags); }
   grid.sync();
-  const bool prof = bs.prof != nullptr && nfront == 1 && blockIdx.x < 2 && tid == 0;
+  const bool prof = bs.prof != nullptr && front == 0 && lb < 2 && tid == 0;
   long long t0 = prof ? gtime_ns() : 0, acc_t[4] = {0, 0, 0, 0}, sub_t[4] = {0, 0, 0, 0};   // sub_t: [0] clock, [1] factor, [2] inverse, [3] tile
   auto lap = [&](int slot) { if (prof) { const long long t1 = gtime_ns(); acc_t[slot] += t1 - t0; t0 = t1; } };
   for (int it = 0; it < iters; ++it) {
@@ -511,9 +511,9 @@ __global__ void __launch_bounds__(kCholThreads, 1) k_band_cholesky(BandSystem bs
     grid.sync();
     lap(3);
   }
-  if (prof) for (int k = 0; k < 4; ++k) bs.prof[4 * blockIdx.x + k] = acc_t[k];
-  if (prof && blockIdx.x == 0) bs.prof[8] = sub_t[3];
-  if (prof && blockIdx.x == 1) { bs.prof[9] = sub_t[0]; bs.prof[10] = sub_t[1]; bs.prof[11] = sub_t[2]; bs.prof[12] = sub_t[3]; }
+  if (prof) for (int k = 0; k < 4; ++k) bs.prof[4 * lb + k] = acc_t[k];
+  if (prof && lb == 0) bs.prof[8] = sub_t[3];
+  if (prof && lb == 1) { bs.prof[9] = sub_t[0]; bs.prof[10] = sub_t[1]; bs.prof[11] = sub_t[2]; bs.prof[12] = sub_t[3]; }
 }
 
 // Two-front factorisation, between the fronts and the separator: the backward front's trailing block (its Schur
