@@ -125,6 +125,7 @@ struct BandSystem {
   int n_known = 0;                 // trailing rows whose solution is given in xt (the separator, solved on the other front)
   int g_lo = 0, g_hi = 0;          // global rows whose right-hand side this front carries (others start at zero)
   double* xt = nullptr;            // [n_glob] solution in time order, shared by the fronts
+  int write_x = 1;                 // back-substitution writes the solution in pose order (off: only xt; a front per GPU, odd ranks' separator)
 };
 
 // Where element (i, j), i >= j, of the time-ordered reduced system lives: the forward storage for the columns left of

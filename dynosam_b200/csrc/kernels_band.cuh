@@ -75,6 +75,11 @@ __global__ void k_band_pad_identity_front(BandSystem bs, int count) {
   for (int i = threadIdx.x; i < count; i += blockDim.x) bs.S[(size_t)i * bs.ld + bs.bw] = 1.0;
 }
 
+__global__ void __launch_bounds__(256) k_scale(double* __restrict__ v, size_t n, double f) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) v[i] *= f;
+}
+
 // scal[dst] = sum v[i]^2 (single block)
 __global__ void __launch_bounds__(1024) k_norm2(int n, const double* __restrict__ v, double* __restrict__ scal, int dst) {
   double s = 0;

@@ -244,10 +244,14 @@ __device__ __noinline__ void chol_diag64(const BandSystem& bs, int j0, double* _
 // off the factorisation's critical path: 8 x 8 diagonal blocks by substitution, then
 // [A 0; B C]^-1 = [A^-1 0; -C^-1 B A^-1  C^-1] for block sizes 8, 16, 32.
 constexpr int kInvSmemBytes = 3 * 64 * 65 * (int)sizeof(double);
-__global__ void __launch_bounds__(256) k_band_diag_inverse(BandSystem bs) {
+__device__ __forceinline__ void band_diag_inverse_block(const BandSystem& bs, int blk);
+__global__ void __launch_bounds__(256) k_band_diag_inverse(BandSystem bs) { band_diag_inverse_block(bs, blockIdx.x); }
+// the same for the blocks from `first` on (the separator's)
+__global__ void __launch_bounds__(256) k_band_diag_inverse_from(BandSystem bs, int first) { band_diag_inverse_block(bs, first + blockIdx.x); }
+__device__ __forceinline__ void band_diag_inverse_block(const BandSystem& bs, int blk) {
   extern __shared__ double inv_smem[];
   double* D = inv_smem; double* Li = D + 64 * 65; double* Tm = Li + 64 * 65;
-  const int tid = threadIdx.x, j0 = blockIdx.x * 64;
+  const int tid = threadIdx.x, j0 = blk * 64;
   const size_t ld = bs.ld;
   const int bw = bs.bw;
   for (int idx = tid; idx < 64 * 64; idx += 256) {
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(256) k_band_diag_inverse(BandSystem bs) {
     }
     __syncthreads();
   }
-  double* out = bs.Linv + (size_t)blockIdx.x * 4096;
+  double* out = bs.Linv + (size_t)blk * 4096;
   for (int idx = tid; idx < 64 * 64; idx += 256) out[idx] = Li[(idx >> 6) * 65 + (idx & 63)];
 }
 
@@ -607,7 +611,7 @@ __global__ void __launch_bounds__(kBackThreads) k_band_backsolve(BandSystem bs0,
       xs[tid] = v;
       if (lb == 0 && !known) {
         if (bs.xt) bs.xt[gi] = v;
-        if (gi < bs.n) {
+        if (gi < bs.n && bs.write_x) {
           const int p = gi / 6, cc = gi - 6 * p;
           double* dst = x + 6 * (size_t)bs.pos_pose[p] + cc;
           *dst = add_to_x ? *dst + v : v;

@@ -47,8 +47,9 @@ def test_two_ranks_match_single_gpu():
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    nproc = 4 if torch.cuda.device_count() >= 4 else 2      # four ranks also exercise the 2 / world scaling of the front-per-GPU exchange
     env = dict(os.environ, OMP_NUM_THREADS="4")
-    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29581",
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1", "--master-port", "29581",
                           os.path.join(ROOT, "tests", "sharded_worker.py")], capture_output=True, text=True, env=env, timeout=900)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     line = [l for l in res.stdout.splitlines() if l.startswith("SHARDED_REPORT ")][-1]
