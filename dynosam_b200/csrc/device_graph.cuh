@@ -64,6 +64,14 @@ struct DeviceGraph {
   const int* pose_ter_ptr = nullptr; const int* pose_ter_idx = nullptr;  // slots (cur point of the factor)
   const int* pose_btw_ptr = nullptr; const int* pose_btw_idx = nullptr;  // factor*2 + role
   const int* pose_pri_ptr = nullptr; const int* pose_pri_idx = nullptr;
+  // pose-side gathers (k_build_poses, k_pose_apply) run one warp per SEGMENT: at most kPoseSegLen point-factor incidences of
+  // one pose (its PoseToPoint list followed by its ternary list). A camera pose with thousands of factors is several
+  // segments whose partial sums a small second kernel adds up in order; a pose with one segment writes its result itself.
+  int n_seg = 0, n_multi = 0;
+  const int* seg_pose = nullptr;       // [n_seg]
+  const int* seg_lo = nullptr;         // [n_seg] first incidence of the segment within the pose's concatenated list
+  const int* pose_seg_ptr = nullptr;   // [n_pose + 1] segments of a pose (consecutive)
+  const int* multi_pose = nullptr;     // [n_multi] poses with more than one segment
 };
 
 // Per-linearisation cache and normal-equation blocks.
@@ -104,6 +112,8 @@ struct DeviceWork {
 constexpr int kBandNB = 64;     // Cholesky panel width (scalars)
 constexpr int kBandTile = 64;   // trailing-update tile edge
 constexpr int kSolveNB = 32;    // block size of the triangular solves
+constexpr int kPoseSegLen = 256;
+
 struct BandSystem {
   int n = 0, n_pad = 0, bw = 0, ld = 0, window = 0;  // window = rows below a panel that it can touch (multiple of kBandTile)
   const int* pose_pos = nullptr;   // [n_pose] position of pose a in time order

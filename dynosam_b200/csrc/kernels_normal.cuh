@@ -36,16 +36,19 @@ __device__ __forceinline__ int ut6(int r, int c) { return r * 6 - (r * (r - 1)) 
 __global__ void __launch_bounds__(256) k_build_poses(DeviceGraph g, const double* __restrict__ pt_lin,
                                                      const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
                                                      const double* __restrict__ btw_J, const double* __restrict__ pri_r,
-                                                     double* __restrict__ App, double* __restrict__ gp) {
-  const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+                                                     double* __restrict__ App, double* __restrict__ gp, double* __restrict__ seg_part) {
+  const int sg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (a >= g.n_pose) return;
+  if (sg >= g.n_seg) return;
+  const int a = g.seg_pose[sg], lo = g.seg_lo[sg], hi = lo + kPoseSegLen;
+  const int n1 = g.pose_p2p_ptr[a + 1] - g.pose_p2p_ptr[a], n2 = g.pose_ter_ptr[a + 1] - g.pose_ter_ptr[a];
+  const bool alone = g.pose_seg_ptr[a + 1] - g.pose_seg_ptr[a] == 1;
   double acc[21], gr[6];
 #pragma unroll
   for (int i = 0; i < 21; ++i) acc[i] = 0;
 #pragma unroll
   for (int i = 0; i < 6; ++i) gr[i] = 0;
-  for (int k = g.pose_p2p_ptr[a] + lane; k < g.pose_p2p_ptr[a + 1]; k += 32) {
+  for (int k = g.pose_p2p_ptr[a] + min(lo, n1) + lane; k < g.pose_p2p_ptr[a] + min(hi, n1); k += 32) {
     const int e = g.pose_p2p_idx[k];
     const double4 c = p2p_qw[e];
     const V3 q = v3(c.x, c.y, c.z);
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(256) k_build_poses(DeviceGraph g, const double
     gr[0] -= c.w * exq.x; gr[1] -= c.w * exq.y; gr[2] -= c.w * exq.z;
     gr[3] += c.w * ev.x;  gr[4] += c.w * ev.y;  gr[5] += c.w * ev.z;
   }
-  for (int k = g.pose_ter_ptr[a] + lane; k < g.pose_ter_ptr[a + 1]; k += 32) {
+  for (int k = g.pose_ter_ptr[a] + max(lo - n1, 0) + lane; k < g.pose_ter_ptr[a] + min(max(hi - n1, 0), n2); k += 32) {
     const int s = g.pose_ter_idx[k];
     const double4 c = ter_qw[s];
     const V3 q = v3(c.x, c.y, c.z);
@@ -67,24 +70,26 @@ __global__ void __launch_bounds__(256) k_build_poses(DeviceGraph g, const double
     gr[0] -= c.w * qxe.x; gr[1] -= c.w * qxe.y; gr[2] -= c.w * qxe.z;
     gr[3] -= c.w * ev.x;  gr[4] -= c.w * ev.y;  gr[5] -= c.w * ev.z;
   }
-  for (int k = g.pose_btw_ptr[a] + lane; k < g.pose_btw_ptr[a + 1]; k += 32) {
-    const int fr = g.pose_btw_idx[k];
-    const double* rec = btw_J + 78 * (size_t)(fr >> 1);
-    const double* J = rec + ((fr & 1) ? 42 : 6);
-    for (int r = 0; r < 6; ++r)
-      for (int c = r; c < 6; ++c) {
-        double s = 0;
-        for (int m = 0; m < 6; ++m) s += J[6 * m + r] * J[6 * m + c];
-        acc[ut6(r, c)] += s;
+  if (lo == 0) {   // the pose-only factors ride with the first segment
+    for (int k = g.pose_btw_ptr[a] + lane; k < g.pose_btw_ptr[a + 1]; k += 32) {
+      const int fr = g.pose_btw_idx[k];
+      const double* rec = btw_J + 78 * (size_t)(fr >> 1);
+      const double* J = rec + ((fr & 1) ? 42 : 6);
+      for (int r = 0; r < 6; ++r)
+        for (int c = r; c < 6; ++c) {
+          double s = 0;
+          for (int m = 0; m < 6; ++m) s += J[6 * m + r] * J[6 * m + c];
+          acc[ut6(r, c)] += s;
+        }
+      for (int r = 0; r < 6; ++r) { double s = 0; for (int m = 0; m < 6; ++m) s += J[6 * m + r] * rec[m]; gr[r] -= s; }
+    }
+    for (int k = g.pose_pri_ptr[a] + lane; k < g.pose_pri_ptr[a + 1]; k += 32) {
+      const int f = g.pose_pri_idx[k];
+      for (int r = 0; r < 6; ++r) {
+        const double is = g.pri_isig[6 * (size_t)f + r];
+        acc[ut6(r, r)] += is * is;
+        gr[r] -= is * pri_r[6 * (size_t)f + r];
       }
-    for (int r = 0; r < 6; ++r) { double s = 0; for (int m = 0; m < 6; ++m) s += J[6 * m + r] * rec[m]; gr[r] -= s; }
-  }
-  for (int k = g.pose_pri_ptr[a] + lane; k < g.pose_pri_ptr[a + 1]; k += 32) {
-    const int f = g.pose_pri_idx[k];
-    for (int r = 0; r < 6; ++r) {
-      const double is = g.pri_isig[6 * (size_t)f + r];
-      acc[ut6(r, r)] += is * is;
-      gr[r] -= is * pri_r[6 * (size_t)f + r];
     }
   }
 #pragma unroll
@@ -92,10 +97,34 @@ __global__ void __launch_bounds__(256) k_build_poses(DeviceGraph g, const double
 #pragma unroll
   for (int i = 0; i < 6; ++i) gr[i] = warp_sum(gr[i]);
   if (lane == 0) {
-    double* A = App + 36 * (size_t)a;
-    for (int r = 0; r < 6; ++r)
-      for (int c = r; c < 6; ++c) { A[6 * r + c] = acc[ut6(r, c)]; A[6 * c + r] = acc[ut6(r, c)]; }
-    for (int i = 0; i < 6; ++i) gp[6 * (size_t)a + i] = gr[i];
+    if (alone) {
+      double* A = App + 36 * (size_t)a;
+      for (int r = 0; r < 6; ++r)
+        for (int c = r; c < 6; ++c) { A[6 * r + c] = acc[ut6(r, c)]; A[6 * c + r] = acc[ut6(r, c)]; }
+      for (int i = 0; i < 6; ++i) gp[6 * (size_t)a + i] = gr[i];
+    } else {
+      double* o = seg_part + 27 * (size_t)sg;
+      for (int i = 0; i < 21; ++i) o[i] = acc[i];
+      for (int i = 0; i < 6; ++i) o[21 + i] = gr[i];
+    }
+  }
+}
+
+// poses with several segments: the partial sums in segment order (one warp per pose)
+__global__ void __launch_bounds__(256) k_build_poses_combine(DeviceGraph g, const double* __restrict__ seg_part, double* __restrict__ App, double* __restrict__ gp) {
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= g.n_multi) return;
+  const int a = g.multi_pose[w];
+  double v = 0.0;
+  if (lane < 27) for (int sg = g.pose_seg_ptr[a]; sg < g.pose_seg_ptr[a + 1]; ++sg) v += seg_part[27 * (size_t)sg + lane];
+  if (lane < 21) {
+    int r = 0, i = lane;
+    while (i >= 6 - r) { i -= 6 - r; ++r; }   // upper-triangular index -> (r, r + i)
+    const int c = r + i;
+    App[36 * (size_t)a + 6 * r + c] = v; App[36 * (size_t)a + 6 * c + r] = v;
+  } else if (lane < 27) {
+    gp[6 * (size_t)a + lane - 21] = v;
   }
 }
 

@@ -89,18 +89,36 @@ __global__ void __launch_bounds__(128) k_chain_apply(DeviceGraph g, const double
 }
 
 // out_a = sg * g_a + sx * [ (A_aa + lambda I) x_a + sum_between J_a^T J_o x_o ] - sum_f J_{f,a}^T J_{f,pts} u_pts
+// One warp per segment of a pose's incidences (DeviceGraph); a pose with several segments leaves partial sums for
+// k_pose_apply_combine, which adds them in order and applies the pose-local terms.
+__device__ __forceinline__ void pose_apply_finish(int a, int lane, double v, double lambda, const double* __restrict__ App, const double* __restrict__ gp,
+                                                  const double* __restrict__ x, double sg, double sx, double* __restrict__ out) {
+  if (sx != 0.0) {
+    const double* A = App + 36 * (size_t)a + 6 * lane;
+    const double* xa = x + 6 * (size_t)a;
+    double s = lambda * xa[lane];
+    for (int c = 0; c < 6; ++c) s += A[c] * xa[c];
+    v += sx * s;
+  }
+  if (sg != 0.0) v += sg * gp[6 * (size_t)a + lane];
+  out[6 * (size_t)a + lane] = v;
+}
+
 __global__ void __launch_bounds__(256) k_pose_apply(DeviceGraph g, double lambda, const double* __restrict__ pose_lin,
                                                     const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw, const int* __restrict__ p2p_slot,
                                                     const double* __restrict__ btw_J, const double* __restrict__ App, const double* __restrict__ gp,
                                                     const double* __restrict__ x, const double* __restrict__ u, double sg, double sx,
-                                                    double* __restrict__ out, const double* __restrict__ done) {
+                                                    double* __restrict__ out, const double* __restrict__ done, double* __restrict__ seg_part) {
   if (done && *done != 0.0) return;
-  const int a = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int seg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (a >= g.n_pose) return;
+  if (seg >= g.n_seg) return;
+  const int a = g.seg_pose[seg], lo = g.seg_lo[seg], hi = lo + kPoseSegLen;
+  const int n1 = g.pose_p2p_ptr[a + 1] - g.pose_p2p_ptr[a], n2 = g.pose_ter_ptr[a + 1] - g.pose_ter_ptr[a];
+  const bool alone = g.pose_seg_ptr[a + 1] - g.pose_seg_ptr[a] == 1;
   double acc[6] = {0, 0, 0, 0, 0, 0};
   M3 R; for (int i = 0; i < 9; ++i) R.a[i] = pose_lin[12 * (size_t)a + i];
-  for (int k = g.pose_p2p_ptr[a] + lane; k < g.pose_p2p_ptr[a + 1]; k += 32) {
+  for (int k = g.pose_p2p_ptr[a] + min(lo, n1) + lane; k < g.pose_p2p_ptr[a] + min(hi, n1); k += 32) {
     const int e = g.pose_p2p_idx[k];
     const double4 qw = p2p_qw[e];
     const double4 uv = *reinterpret_cast<const double4*>(u + 4 * (size_t)p2p_slot[e]);
@@ -109,7 +127,7 @@ __global__ void __launch_bounds__(256) k_pose_apply(DeviceGraph g, double lambda
     acc[0] -= qw.w * yxq.x; acc[1] -= qw.w * yxq.y; acc[2] -= qw.w * yxq.z;
     acc[3] += qw.w * y.x;   acc[4] += qw.w * y.y;   acc[5] += qw.w * y.z;
   }
-  for (int k = g.pose_ter_ptr[a] + lane; k < g.pose_ter_ptr[a + 1]; k += 32) {
+  for (int k = g.pose_ter_ptr[a] + max(lo - n1, 0) + lane; k < g.pose_ter_ptr[a] + min(max(hi - n1, 0), n2); k += 32) {
     const int s = g.pose_ter_idx[k];
     const double4 qw = ter_qw[s];
     const double4 ui = *reinterpret_cast<const double4*>(u + 4 * (size_t)(s - 32));
@@ -119,7 +137,7 @@ __global__ void __launch_bounds__(256) k_pose_apply(DeviceGraph g, double lambda
     acc[0] -= qw.w * qxy.x; acc[1] -= qw.w * qxy.y; acc[2] -= qw.w * qxy.z;
     acc[3] -= qw.w * y.x;   acc[4] -= qw.w * y.y;   acc[5] -= qw.w * y.z;
   }
-  if (sx != 0.0) {
+  if (sx != 0.0 && lo == 0) {
     for (int k = g.pose_btw_ptr[a] + lane; k < g.pose_btw_ptr[a + 1]; k += 32) {
       const int fr = g.pose_btw_idx[k];
       const int f = fr >> 1, role = fr & 1;
@@ -135,17 +153,22 @@ __global__ void __launch_bounds__(256) k_pose_apply(DeviceGraph g, double lambda
 #pragma unroll
   for (int i = 0; i < 6; ++i) acc[i] = warp_sum(acc[i]);
   if (lane < 6) {
-    double v = acc[lane];
-    if (sx != 0.0) {
-      const double* A = App + 36 * (size_t)a + 6 * lane;
-      const double* xa = x + 6 * (size_t)a;
-      double s = lambda * xa[lane];
-      for (int c = 0; c < 6; ++c) s += A[c] * xa[c];
-      v += sx * s;
-    }
-    if (sg != 0.0) v += sg * gp[6 * (size_t)a + lane];
-    out[6 * (size_t)a + lane] = v;
+    if (alone) pose_apply_finish(a, lane, acc[lane], lambda, App, gp, x, sg, sx, out);
+    else seg_part[6 * (size_t)seg + lane] = acc[lane];
   }
+}
+
+__global__ void __launch_bounds__(256) k_pose_apply_combine(DeviceGraph g, double lambda, const double* __restrict__ App, const double* __restrict__ gp,
+                                                            const double* __restrict__ x, double sg, double sx, double* __restrict__ out,
+                                                            const double* __restrict__ done, const double* __restrict__ seg_part) {
+  if (done && *done != 0.0) return;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= g.n_multi || lane >= 6) return;
+  const int a = g.multi_pose[w];
+  double v = 0.0;
+  for (int seg = g.pose_seg_ptr[a]; seg < g.pose_seg_ptr[a + 1]; ++seg) v += seg_part[6 * (size_t)seg + lane];
+  pose_apply_finish(a, lane, v, lambda, App, gp, x, sg, sx, out);
 }
 
 // ---- PCG vector kernels: single block, n = 6 * n_pose entries ----------

@@ -23,9 +23,13 @@ inline void LmSolver::pass_linearize() {
   launch_check("k_reduce_partials");
   static_assert(kLinOld == kErr + 1, "kErr and kLinOld are reduced together");
   comm_.sum(w_.scal + kErr, 2, stream_);
-  const int blocks = std::max(1, (g_.n_pose * 32 + 255) / 256);
-  k_build_poses<<<blocks, 256, 0, stream_>>>(g_, w_.pt_lin, w_.p2p_qw, w_.ter_qw, w_.btw_J, w_.pri_r, w_.App, w_.gp);
+  const int blocks = std::max(1, (g_.n_seg * 32 + 255) / 256);
+  k_build_poses<<<blocks, 256, 0, stream_>>>(g_, w_.pt_lin, w_.p2p_qw, w_.ter_qw, w_.btw_J, w_.pri_r, w_.App, w_.gp, d_seg_part_.p);
   launch_check("k_build_poses");
+  if (g_.n_multi) {
+    k_build_poses_combine<<<(g_.n_multi * 32 + 255) / 256, 256, 0, stream_>>>(g_, d_seg_part_.p, w_.App, w_.gp);
+    launch_check("k_build_poses_combine");
+  }
   linearized_ = true;
   timing_[7] += 1;
 }
@@ -39,6 +43,17 @@ inline void LmSolver::pass_factorize(double lambda) {
   const int pb = std::max(1, (g_.n_pose * 32 + 255) / 256);
   k_schur_diag<<<pb, 256, 0, stream_>>>(g_, lambda, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, w_.App, w_.Sig, w_.SigOff, w_.Pinv, w_.flags);
   launch_check("k_schur_diag");
+}
+
+// out = sg * g_p + sx * (A_pp + lambda I) x [+ between terms] - W^T u : one warp per segment of a pose's incidences, then the
+// poses with several segments are summed up
+inline void LmSolver::pose_apply(double lambda, const double* x, const double* u, double sg, double sx, double* out, const double* done, const char* what) {
+  k_pose_apply<<<std::max(1, (g_.n_seg * 32 + 255) / 256), 256, 0, stream_>>>(g_, lambda, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, w_.btw_J, w_.App, w_.gp, x, u, sg, sx, out, done, d_seg_part_.p);
+  launch_check(what);
+  if (g_.n_multi) {
+    k_pose_apply_combine<<<(g_.n_multi * 32 + 255) / 256, 256, 0, stream_>>>(g_, lambda, w_.App, w_.gp, x, sg, sx, out, done, d_seg_part_.p);
+    launch_check("k_pose_apply_combine");
+  }
 }
 
 inline void LmSolver::read_scalars() {
@@ -56,8 +71,7 @@ inline int LmSolver::pass_pcg(double lambda) {
   // rhs = g_p - W^T M^-1 g_pt
   k_chain_apply<<<cb, 128, 0, stream_>>>(g_, w_.pose_lin, w_.p2p_qw, w_.ter_qw, w_.gpt, w_.B, w_.Dinv, nullptr, 1.0, 0.0, w_.u, nullptr);
   launch_check("k_chain_apply(rhs)");
-  k_pose_apply<<<pb, 256, 0, stream_>>>(g_, lambda, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, w_.btw_J, w_.App, w_.gp, nullptr, w_.u, 1.0, 0.0, w_.rhs, nullptr);
-  launch_check("k_pose_apply(rhs)");
+  pose_apply(lambda, nullptr, w_.u, 1.0, 0.0, w_.rhs, nullptr, "k_pose_apply(rhs)");
   k_pcg_init<<<1, 1024, 0, stream_>>>(n, w_.rhs, w_.Pinv, w_.x, w_.r, w_.z, w_.p, w_.scal);
   launch_check("k_pcg_init");
   const double tol2 = params_.pcg_rel_tol * params_.pcg_rel_tol;
@@ -69,8 +83,7 @@ inline int LmSolver::pass_pcg(double lambda) {
     for (int i = 0; i < todo; ++i) {
       k_chain_apply<<<cb, 128, 0, stream_>>>(g_, w_.pose_lin, w_.p2p_qw, w_.ter_qw, w_.gpt, w_.B, w_.Dinv, w_.p, 0.0, 1.0, w_.u, w_.scal + kDone);
       launch_check("k_chain_apply");
-      k_pose_apply<<<pb, 256, 0, stream_>>>(g_, lambda, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, w_.btw_J, w_.App, w_.gp, w_.p, w_.u, 0.0, 1.0, w_.Ap, w_.scal + kDone);
-      launch_check("k_pose_apply");
+      pose_apply(lambda, w_.p, w_.u, 0.0, 1.0, w_.Ap, w_.scal + kDone, "k_pose_apply");
       k_pcg_update<<<1, 1024, 0, stream_>>>(n, w_.Pinv, w_.Ap, w_.x, w_.r, w_.z, w_.p, w_.scal, tol2);
       launch_check("k_pcg_update");
     }
@@ -140,8 +153,7 @@ inline int LmSolver::pass_band(double lambda) {
   // rhs = g_p - W^T M^-1 g_pt, loaded in time order so that the factorisation carries L^-1 rhs along
   k_chain_apply<<<cb, 128, 0, stream_>>>(g_, w_.pose_lin, w_.p2p_qw, w_.ter_qw, w_.gpt, w_.B, w_.Dinv, nullptr, 1.0, 0.0, w_.u, nullptr);
   launch_check("k_chain_apply(rhs)");
-  k_pose_apply<<<pb, 256, 0, stream_>>>(g_, lambda, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, w_.btw_J, w_.App, w_.gp, nullptr, w_.u, 1.0, 0.0, w_.rhs, nullptr);
-  launch_check("k_pose_apply(rhs)");
+  pose_apply(lambda, nullptr, w_.u, 1.0, 0.0, w_.rhs, nullptr, "k_pose_apply(rhs)");
   comm_.sum(w_.rhs, (size_t)n, stream_);
   k_norm2<<<1, 1024, 0, stream_>>>(n, w_.rhs, w_.scal, kRhsNorm2);
   launch_check("k_norm2");
@@ -259,8 +271,7 @@ inline int LmSolver::pass_band(double lambda) {
     // dpt = M^-1 (g_pt - W x) and res = rhs - S x in one application of the operator
     k_chain_apply<<<cb, 128, 0, stream_>>>(g_, w_.pose_lin, w_.p2p_qw, w_.ter_qw, w_.gpt, w_.B, w_.Dinv, w_.x, 1.0, -1.0, w_.dpt, nullptr);
     launch_check("k_chain_apply(backsub)");
-    k_pose_apply<<<pb, 256, 0, stream_>>>(g_, lambda_pose, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, w_.btw_J, w_.App, w_.gp, w_.x, w_.dpt, 1.0, -1.0, d_res_.p, nullptr);
-    launch_check("k_pose_apply(residual)");
+    pose_apply(lambda_pose, w_.x, w_.dpt, 1.0, -1.0, d_res_.p, nullptr, "k_pose_apply(residual)");
     comm_.sum(d_res_.p, (size_t)n, stream_);
     comm_.max(w_.flags, 4, stream_);           // a chain or band pivot failure on any rank fails the trial on all
     k_norm2<<<1, 1024, 0, stream_>>>(n, d_res_.p, w_.scal, kResNorm2);
