@@ -64,6 +64,7 @@ struct DeviceGraph {
   const int* pose_ter_ptr = nullptr; const int* pose_ter_idx = nullptr;  // slots (cur point of the factor)
   const int* pose_btw_ptr = nullptr; const int* pose_btw_idx = nullptr;  // factor*2 + role
   const int* pose_pri_ptr = nullptr; const int* pose_pri_idx = nullptr;
+  const int* pose_p2p_nstatic = nullptr;   // [n_pose] leading entries of pose_p2p_idx whose point is a chain of one (static landmarks)
   // pose-side gathers (k_build_poses, k_pose_apply) run one warp per SEGMENT: at most kPoseSegLen point-factor incidences of
   // one pose (its PoseToPoint list followed by its ternary list). A camera pose with thousands of factors is several
   // segments whose partial sums a small second kernel adds up in order; a pose with one segment writes its result itself.

@@ -316,6 +316,8 @@ class LmSolver {
   DevBuf<int> d_pose_p2p_ptr_, d_pose_p2p_idx_, d_pose_ter_ptr_, d_pose_ter_idx_, d_pose_btw_ptr_, d_pose_btw_idx_, d_pose_pri_ptr_, d_pose_pri_idx_;
   DevBuf<int> d_p2p_entry_of_input_, d_ter_slot_of_input_;
   DevBuf<int> d_seg_pose_, d_seg_lo_, d_pose_seg_ptr_, d_multi_pose_;   // segments of the pose-side gathers
+  DevBuf<int> d_pose_nstatic_;
+  int static_dmax_ = 0, static_both_sides_ = 0;
   DevBuf<double> d_seg_part_;                                           // [n_seg][27] partial sums of the poses with several segments
   // work
   DevBuf<double> d_pose_a_, d_pose_b_, d_pt_a_, d_pt_b_, d_pose0_, d_pt0_;

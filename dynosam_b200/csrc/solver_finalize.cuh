@@ -120,6 +120,8 @@ inline void LmSolver::finalize() {
     for (int i = 0; i < n_items; ++i) { const int a = pose_of_item(i); if (a >= 0) idx[cur[a]++] = value_of_item(i); }
   };
   std::vector<int> pp_ptr, pp_idx, pt_ptr, pt_idx, pb_ptr, pb_idx, pr_ptr, pr_idx;
+  std::vector<int> pose_nstatic(np, 0);   // leading entries of a pose's PoseToPoint list whose point is a chain of one (static landmarks)
+  static_dmax_ = 0;
   {
     // Within a pose, keep the PoseToPoint incidences of one object's tracklets together, and within an object order them
     // by how far the point sits from its chain head (the length of the head-ward walk), deepest first: the lanes of a warp
@@ -138,6 +140,7 @@ inline void LmSolver::finalize() {
     }
     int max_depth = 1;
     for (int sl = 0; sl < n_slices; ++sl) max_depth = std::max(max_depth, slice_len[sl]);
+    for (int c = 0; c < n_chains; ++c) if (chain_group[c] == 0) static_dmax_ = std::max(static_dmax_, degree[chains[c].head]);
     auto chain_of_slot = [&](int slot) { return slot_chain[slot]; };
     auto depth = [&](int slot) { return (slot - slice_base[slot_chain[slot] >> 5]) >> 5; };
     // CSR in insertion order first (two linear passes), then every pose list is sorted on its own, in parallel, by
@@ -151,7 +154,11 @@ inline void LmSolver::finalize() {
       for (int e = 0; e < n_entries; ++e) {
         if (p2p_pose[e] < 0) continue;
         const int slot = p2p_slot[e];
-        const unsigned long long key = ((unsigned long long)chain_group[chain_of_slot(slot)] << 44) | ((unsigned long long)(max_depth - 1 - depth(slot)) << 28);
+        // static landmarks (group 0, depth 0): by the observation's place in the landmark's own list, latest first, so that the
+        // observations that have a partner o places back form a prefix of the pose's list (k_schur_static)
+        const int grp = chain_group[chain_of_slot(slot)];
+        const unsigned long long sub = grp == 0 ? (unsigned long long)(65535 - std::min(65535, (e - row_base[slot >> 5]) >> 5)) : (unsigned long long)(max_depth - 1 - depth(slot));
+        const unsigned long long key = ((unsigned long long)grp << 44) | (sub << 28);
         const int at = cur[p2p_pose[e]]++;
         pp_key[at] = key | (unsigned long long)(at - pp_ptr[p2p_pose[e]]);   // low 28 bits: rank within the pose (insertion order)
       }
@@ -165,7 +172,12 @@ inline void LmSolver::finalize() {
 #pragma omp parallel for schedule(dynamic, 16)
       for (int a = 0; a < np; ++a) {
         std::sort(pp_key.begin() + pp_ptr[a], pp_key.begin() + pp_ptr[a + 1]);
-        for (int i = pp_ptr[a]; i < pp_ptr[a + 1]; ++i) pp_idx[i] = by_rank[pp_ptr[a] + (int)(pp_key[i] & 0xfffffffull)];
+        int ns = 0;
+        for (int i = pp_ptr[a]; i < pp_ptr[a + 1]; ++i) {
+          pp_idx[i] = by_rank[pp_ptr[a] + (int)(pp_key[i] & 0xfffffffull)];
+          if ((pp_key[i] >> 44) == 0) ++ns;   // group 0 sorts first
+        }
+        pose_nstatic[a] = ns;
       }
     }
     // stable counting sort of `items` by key(item) in [0, n_keys)
@@ -218,6 +230,7 @@ inline void LmSolver::finalize() {
   d_pose_btw_ptr_.upload(pb_ptr, stream_); d_pose_btw_idx_.upload(pb_idx, stream_);
   d_pose_pri_ptr_.upload(pr_ptr, stream_); d_pose_pri_idx_.upload(pr_idx, stream_);
   d_p2p_entry_of_input_.upload(p2p_entry_of_input_, stream_); d_ter_slot_of_input_.upload(ter_slot_of_input_, stream_);
+  d_pose_nstatic_.upload(pose_nstatic, stream_);
   d_seg_pose_.upload(seg_pose, stream_); d_seg_lo_.upload(seg_lo, stream_); d_pose_seg_ptr_.upload(pose_seg_ptr, stream_); d_multi_pose_.upload(multi_pose, stream_);
   // state
   auto& pt4 = hs_pt4_; pt4.assign((size_t)n_slots * 4, 0.0);
@@ -266,6 +279,7 @@ inline void LmSolver::finalize() {
   g_.pri_a = d_pri_a_.p; g_.pri_z = d_pri_z_.p; g_.pri_isig = d_pri_isig_.p;
   g_.pose_p2p_ptr = d_pose_p2p_ptr_.p; g_.pose_p2p_idx = d_pose_p2p_idx_.p; g_.pose_ter_ptr = d_pose_ter_ptr_.p; g_.pose_ter_idx = d_pose_ter_idx_.p;
   g_.pose_btw_ptr = d_pose_btw_ptr_.p; g_.pose_btw_idx = d_pose_btw_idx_.p; g_.pose_pri_ptr = d_pose_pri_ptr_.p; g_.pose_pri_idx = d_pose_pri_idx_.p;
+  g_.pose_p2p_nstatic = d_pose_nstatic_.p;
   g_.n_seg = (int)seg_pose.size(); g_.n_multi = (int)multi_pose.size();
   g_.seg_pose = d_seg_pose_.p; g_.seg_lo = d_seg_lo_.p; g_.pose_seg_ptr = d_pose_seg_ptr_.p; g_.multi_pose = d_multi_pose_.p;
   d_seg_part_.alloc(27 * seg_pose.size());
@@ -303,6 +317,18 @@ inline void LmSolver::setup_band(const std::vector<int>& chain_of_point) {
   std::iota(pos_pose.begin(), pos_pose.end(), 0);
   std::stable_sort(pos_pose.begin(), pos_pose.end(), [&](int x, int y) { return when[x] < when[y]; });
   for (int p = 0; p < np; ++p) pose_pos[pos_pose[p]] = p;
+  // are the PoseToPoint factors of every point in ascending time order (the order the reference emits them in)? The static
+  // assembly then only looks back along a landmark's observations.
+  {
+    std::vector<int> last_pos(point_keys_.size(), -1);
+    static_both_sides_ = 0;
+    for (size_t f = 0; f < in_p2p_pose_.size(); ++f) {
+      int& lp = last_pos[in_p2p_point_[f]];
+      const int ps = pose_pos[in_p2p_pose_[f]];
+      if (ps < lp) { static_both_sides_ = 1; break; }
+      lp = ps;
+    }
+  }
   // envelope: every pose of a point chain reaches back to the chain's earliest pose
   int n_chains = 0;
   for (int c : chain_of_point) n_chains = std::max(n_chains, c + 1);

@@ -138,6 +138,10 @@ inline int LmSolver::pass_band(double lambda) {
   tick(16);
   k_schur_init<<<g_.n_pose, 128, 0, stream_>>>(g_, band_, bm, tw ? 0 : 1, lambda_pose, w_.btw_J, w_.App);
   launch_check("k_schur_init");
+  if (static_dmax_ > 0) {
+    k_schur_static<<<g_.n_pose, kStaticThreads, 0, stream_>>>(g_, band_, bm, w_.pose_lin, w_.p2p_qw, d_p2p_slot_.p, w_.Sig, static_dmax_ - 1, static_both_sides_);
+    launch_check("k_schur_static");
+  }
   k_schur_assemble_warp<<<dim3(g_.n_pose, schur_split_), kSchurThreads, 0, stream_>>>(g_, band_, bm, w_.pose_lin, w_.p2p_qw, w_.ter_qw, d_p2p_slot_.p, d_fwd_min_.p, w_.Sig, w_.G);
   launch_check("k_schur_assemble_warp");
   tick(17);
