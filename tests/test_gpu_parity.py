@@ -252,3 +252,52 @@ def test_two_front_factorisation_matches_single_front(scene_name):
     np.testing.assert_allclose(res[4][5], res[3][5], rtol=1e-9)         # same chi2 trace
     np.testing.assert_allclose(res[4][3], res[3][3], atol=1e-7)
     np.testing.assert_allclose(res[4][4], res[3][4], atol=1e-7)
+
+
+# ---- static-landmark assembly on irregular input: gaps in the tracks, factors handed over out of time order ----
+def _irregular_copy(g, drop_gaps, shuffle, seed=3):
+    from types import SimpleNamespace
+    rng = np.random.default_rng(seed)
+    keep = np.ones(g.n_p2p, dtype=bool)
+    if drop_gaps:
+        # drop every third interior observation of the landmarks with at least five (never the first or the last: no variable
+        # loses its factors), which leaves gaps in the tracks: a partner "o places back" is no longer the same pose for all
+        order = np.argsort(g.p2p_point, kind="stable")
+        pts, start, cnt = np.unique(g.p2p_point[order], return_index=True, return_counts=True)
+        for s, c in zip(start, cnt):
+            if c >= 5:
+                keep[order[s + 1 + rng.integers(0, 2):s + c - 1:3]] = False
+    idx = np.flatnonzero(keep)
+    if shuffle:
+        idx = rng.permutation(idx)          # factors of a point no longer arrive in ascending time
+    c = SimpleNamespace(**{k: getattr(g, k) for k in ("pose_keys", "pose_Rt", "point_keys", "point_xyz", "n_pose", "n_point", "ter_prev", "ter_cur", "ter_motion", "ter_sigma",
+                                                      "ter_huber", "ter_order", "n_ternary", "btw_a", "btw_b", "btw_z", "btw_sigmas", "btw_order", "n_between", "pri_a", "pri_z",
+                                                      "pri_sigmas", "pri_order", "n_prior")})
+    c.p2p_pose, c.p2p_point, c.p2p_z = g.p2p_pose[idx], g.p2p_point[idx], g.p2p_z[idx]
+    c.p2p_sigma, c.p2p_huber, c.p2p_order, c.n_p2p = g.p2p_sigma[idx], g.p2p_huber[idx], g.p2p_order[idx], len(idx)
+    c.n_factors = c.n_p2p + c.n_ternary + c.n_between + c.n_prior
+    c.pose_frames = g.pose_frames
+    return c
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("drop_gaps,shuffle", [(True, False), (False, True), (True, True)])
+def test_static_assembly_on_irregular_tracks(drop_gaps, shuffle):
+    g = _irregular_copy(scenes.small_noisy().full_batch_graph(), drop_gaps, shuffle)
+    gpu = d.GpuLevenbergMarquardt(None)
+    gpu.load_host_arrays(g)
+    ora = OracleGraph.from_graph(g)
+    assert gpu.error() == pytest.approx(ora.error(), rel=1e-12)
+    for lam in (1e-4, 1.0):
+        ok_g, dp_g, dpt_g, _ = gpu.solve_once(lam)
+        ok_c, dp_c, dpt_c = ora.solve_once(lam)
+        assert ok_g and ok_c
+        assert rel_err(dp_g, dp_c) <= 1e-7 and rel_err(dpt_g, dpt_c) <= 1e-7, (lam, rel_err(dp_g, dp_c), rel_err(dpt_g, dpt_c))
+    p = d.default_lm_params()
+    p.max_iterations = 4
+    lm = d.GpuLevenbergMarquardt(None, p)
+    lm.load_host_arrays(g)
+    lm.optimize()
+    r = ora.optimize(max_iterations=4)
+    np.testing.assert_allclose(lm.error_trace, r["error_trace"][:len(lm.error_trace)], rtol=CHI2_RTOL)
+    assert lm.timing()["band_single_front_repeats"] == 0
