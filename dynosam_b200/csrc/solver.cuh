@@ -5,6 +5,7 @@
 // reference call sites src/backend/RGBDBackendModule.cc:220-221, 374-376).
 #pragma once
 #include <cuda_runtime.h>
+#include <omp.h>
 
 #include <algorithm>
 #include <cstdio>

@@ -126,78 +126,81 @@ inline void LmSolver::finalize() {
     // Within a pose, keep the PoseToPoint incidences of one object's tracklets together, and within an object order them
     // by how far the point sits from its chain head (the length of the head-ward walk), deepest first: the lanes of a warp
     // in the Schur assembly then meet the same motion poses at the same step of their chain walks and finish together.
-    // Two stable counting passes over all incidences (depth, then object) followed by a stable bucket fill per pose give
-    // every pose list that order without a comparison sort.
     std::vector<int> chain_group(n_chains, 0);   // 0: static landmark (chain of one)
-    int n_groups = 1;
-    for (int64_t f = 0; f < n_ter; ++f) {
-      int& grp = chain_group[chain_of_point[in_ter_cur_[f]]];
-      if (grp > 0) continue;
+    int max_depth = 1, dmax = 0;
+#pragma omp parallel for schedule(static) reduction(max : dmax)
+    for (int c = 0; c < n_chains; ++c) {
+      const int f = out_link[chains[c].head];   // the first link of the chain names its object
+      if (f < 0) { dmax = std::max(dmax, degree[chains[c].head]); continue; }
       const Key key = pose_keys_[in_ter_motion_[f]];
       const unsigned char ch = key_chr(key);
-      grp = 1 + ((ch == kObjectMotionSymbolChar || ch == kObjectPoseSymbolChar) ? (int)key_label(key) : 256 + in_ter_motion_[f]);
-      n_groups = std::max(n_groups, grp + 1);
+      chain_group[c] = 1 + ((ch == kObjectMotionSymbolChar || ch == kObjectPoseSymbolChar) ? (int)key_label(key) : 256 + in_ter_motion_[f]);
     }
-    int max_depth = 1;
+    static_dmax_ = dmax;
     for (int sl = 0; sl < n_slices; ++sl) max_depth = std::max(max_depth, slice_len[sl]);
-    for (int c = 0; c < n_chains; ++c) if (chain_group[c] == 0) static_dmax_ = std::max(static_dmax_, degree[chains[c].head]);
     auto chain_of_slot = [&](int slot) { return slot_chain[slot]; };
     auto depth = [&](int slot) { return (slot - slice_base[slot_chain[slot] >> 5]) >> 5; };
-    // CSR in insertion order first (two linear passes), then every pose list is sorted on its own, in parallel, by
-    // (object, depth descending, insertion rank): the rank makes the order total, hence deterministic
-    pp_ptr.assign(np + 1, 0);
-    for (int e = 0; e < n_entries; ++e) if (p2p_pose[e] >= 0) pp_ptr[p2p_pose[e] + 1]++;
-    for (int a = 0; a < np; ++a) pp_ptr[a + 1] += pp_ptr[a];
-    std::vector<unsigned long long> pp_key(pp_ptr[np]);
-    {
-      std::vector<int> cur(pp_ptr.begin(), pp_ptr.end() - 1);
-      for (int e = 0; e < n_entries; ++e) {
-        if (p2p_pose[e] < 0) continue;
-        const int slot = p2p_slot[e];
-        // static landmarks (group 0, depth 0): by the observation's place in the landmark's own list, latest first, so that the
-        // observations that have a partner o places back form a prefix of the pose's list (k_schur_static)
-        const int grp = chain_group[chain_of_slot(slot)];
-        const unsigned long long sub = grp == 0 ? (unsigned long long)(65535 - std::min(65535, (e - row_base[slot >> 5]) >> 5)) : (unsigned long long)(max_depth - 1 - depth(slot));
-        const unsigned long long key = ((unsigned long long)grp << 44) | (sub << 28);
-        const int at = cur[p2p_pose[e]]++;
-        pp_key[at] = key | (unsigned long long)(at - pp_ptr[p2p_pose[e]]);   // low 28 bits: rank within the pose (insertion order)
+    // Stable bucketing by pose in two parallel passes: the items are cut into T contiguous pieces, every piece counts its
+    // poses, a prefix over (pose, piece) gives each piece its own range inside every pose's list, and the second pass fills
+    // them. The result is the insertion-order list of every pose, whatever the number of threads that ran.
+    const int T = std::max(1, std::min(32, omp_get_max_threads()));
+    std::vector<int> hist((size_t)T * np);
+    auto bucket_by_pose = [&](int64_t n_items, auto pose_of_item, std::vector<int>& ptr, auto emit) {
+      std::fill(hist.begin(), hist.end(), 0);
+#pragma omp parallel for schedule(static, 1)
+      for (int t = 0; t < T; ++t) {
+        int* h = hist.data() + (size_t)t * np;
+        for (int64_t i = n_items * t / T, hi = n_items * (t + 1) / T; i < hi; ++i) { const int a = pose_of_item(i); if (a >= 0) h[a]++; }
       }
-    }
-    pp_idx.assign(pp_ptr[np], 0);
-    {
-      // entry of (pose, rank): recover it from a second insertion-order pass
-      std::vector<int> by_rank(pp_ptr[np]);
-      std::vector<int> cur(pp_ptr.begin(), pp_ptr.end() - 1);
-      for (int e = 0; e < n_entries; ++e) if (p2p_pose[e] >= 0) by_rank[cur[p2p_pose[e]]++] = e;
-#pragma omp parallel for schedule(dynamic, 16)
+      ptr.assign(np + 1, 0);
+      int run = 0;
       for (int a = 0; a < np; ++a) {
-        std::sort(pp_key.begin() + pp_ptr[a], pp_key.begin() + pp_ptr[a + 1]);
-        int ns = 0;
-        for (int i = pp_ptr[a]; i < pp_ptr[a + 1]; ++i) {
-          pp_idx[i] = by_rank[pp_ptr[a] + (int)(pp_key[i] & 0xfffffffull)];
-          if ((pp_key[i] >> 44) == 0) ++ns;   // group 0 sorts first
-        }
-        pose_nstatic[a] = ns;
+        ptr[a] = run;
+        for (int t = 0; t < T; ++t) { int& h = hist[(size_t)t * np + a]; const int c = h; h = run; run += c; }
       }
-    }
-    // stable counting sort of `items` by key(item) in [0, n_keys)
-    auto counting_sort = [&](std::vector<int>& items, int n_keys, auto key) {
-      std::vector<int> start(n_keys + 1, 0), out(items.size());
-      for (int it : items) start[key(it) + 1]++;
-      for (int k = 0; k < n_keys; ++k) start[k + 1] += start[k];
-      for (int it : items) out[start[key(it)]++] = it;
-      items.swap(out);
+      ptr[np] = run;
+#pragma omp parallel for schedule(static, 1)
+      for (int t = 0; t < T; ++t) {
+        int* h = hist.data() + (size_t)t * np;
+        for (int64_t i = n_items * t / T, hi = n_items * (t + 1) / T; i < hi; ++i) { const int a = pose_of_item(i); if (a >= 0) emit(i, a, h[a]++); }
+      }
     };
-    // ternary incidences of a motion pose: deepest first
-    std::vector<int> ts;
-    ts.reserve(n_ter);
-    for (int sl = 0; sl < n_slots; ++sl) if (ter_motion[sl] >= 0) ts.push_back(sl);
-    counting_sort(ts, max_depth, [&](int sl) { return max_depth - 1 - depth(sl); });
-    pt_ptr.assign(np + 1, 0);
-    for (int sl : ts) pt_ptr[ter_motion[sl] + 1]++;
-    for (int a = 0; a < np; ++a) pt_ptr[a + 1] += pt_ptr[a];
+    // PoseToPoint incidences: every pose list is then sorted on its own, in parallel, by (object, depth descending,
+    // insertion rank): the rank makes the order total, hence deterministic
+    std::vector<unsigned long long> pp_key;
+    std::vector<int> by_rank;   // entry of (pose, insertion rank)
+    pp_key.resize(n_p2p); by_rank.resize(n_p2p);   // one ELL entry per PoseToPoint factor
+    bucket_by_pose(n_entries, [&](int64_t e) { return p2p_pose[e]; }, pp_ptr, [&](int64_t e, int a, int at) {
+      const int slot = p2p_slot[e];
+      // static landmarks (group 0, depth 0): by the observation's place in the landmark's own list, latest first, so that the
+      // observations that have a partner o places back form a prefix of the pose's list (k_schur_static)
+      const int grp = chain_group[chain_of_slot(slot)];
+      const unsigned long long sub = grp == 0 ? (unsigned long long)(65535 - std::min(65535, ((int)e - row_base[slot >> 5]) >> 5)) : (unsigned long long)(max_depth - 1 - depth(slot));
+      pp_key[at] = ((unsigned long long)grp << 44) | (sub << 28) | (unsigned long long)(at - pp_ptr[a]);   // low 28 bits: insertion rank within the pose
+      by_rank[at] = (int)e;
+    });
+    pp_idx.assign(pp_ptr[np], 0);
+#pragma omp parallel for schedule(dynamic, 16)
+    for (int a = 0; a < np; ++a) {
+      std::sort(pp_key.begin() + pp_ptr[a], pp_key.begin() + pp_ptr[a + 1]);
+      int ns = 0;
+      for (int i = pp_ptr[a]; i < pp_ptr[a + 1]; ++i) {
+        pp_idx[i] = by_rank[pp_ptr[a] + (int)(pp_key[i] & 0xfffffffull)];
+        if ((pp_key[i] >> 44) == 0) ++ns;   // group 0 sorts first
+      }
+      pose_nstatic[a] = ns;
+    }
+    // ternary incidences of a motion pose: deepest first, then by slot
+    std::vector<unsigned long long> pt_key(n_ter);
+    bucket_by_pose(n_slots, [&](int64_t sl) { return ter_motion[sl]; }, pt_ptr, [&](int64_t sl, int, int at) {
+      pt_key[at] = ((unsigned long long)(max_depth - 1 - depth((int)sl)) << 32) | (unsigned long long)sl;
+    });
     pt_idx.assign(pt_ptr[np], 0);
-    { std::vector<int> cur(pt_ptr.begin(), pt_ptr.end() - 1); for (int sl : ts) pt_idx[cur[ter_motion[sl]]++] = sl; }
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int a = 0; a < np; ++a) {
+      std::sort(pt_key.begin() + pt_ptr[a], pt_key.begin() + pt_ptr[a + 1]);
+      for (int i = pt_ptr[a]; i < pt_ptr[a + 1]; ++i) pt_idx[i] = (int)(pt_key[i] & 0xffffffffull);
+    }
   }
   lap(3);
   build_csr(2 * n_btw, [&](int i) { return (i & 1) ? h_btw_b_[i >> 1] : h_btw_a_[i >> 1]; }, [&](int i) { return i; }, pb_ptr, pb_idx);
@@ -317,28 +320,40 @@ inline void LmSolver::setup_band(const std::vector<int>& chain_of_point) {
   std::iota(pos_pose.begin(), pos_pose.end(), 0);
   std::stable_sort(pos_pose.begin(), pos_pose.end(), [&](int x, int y) { return when[x] < when[y]; });
   for (int p = 0; p < np; ++p) pose_pos[pos_pose[p]] = p;
+  // order-independent minimum into a shared array from a parallel loop (the value only ever decreases, so nearly every call
+  // is one load once the first factors of a target have been seen)
+  auto atomic_min = [](int* p, int v) {
+    int o = __atomic_load_n(p, __ATOMIC_RELAXED);
+    while (v < o && !__atomic_compare_exchange_n(p, &o, v, true, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) {}
+  };
+  const int64_t n_p2p = (int64_t)in_p2p_pose_.size(), n_ter = (int64_t)in_ter_cur_.size();
   // are the PoseToPoint factors of every point in ascending time order (the order the reference emits them in)? The static
-  // assembly then only looks back along a landmark's observations.
+  // assembly then only looks back along a landmark's observations. The factor before f at the same point is the ELL entry
+  // one row of lanes earlier (same slot).
   {
-    std::vector<int> last_pos(point_keys_.size(), -1);
-    static_both_sides_ = 0;
-    for (size_t f = 0; f < in_p2p_pose_.size(); ++f) {
-      int& lp = last_pos[in_p2p_point_[f]];
-      const int ps = pose_pos[in_p2p_pose_[f]];
-      if (ps < lp) { static_both_sides_ = 1; break; }
-      lp = ps;
+    int both = 0;
+#pragma omp parallel for schedule(static) reduction(| : both)
+    for (int64_t f = 0; f < n_p2p; ++f) {
+      const int e = p2p_entry_of_input_[f];
+      if (e >= 32 && hs_p2p_slot_[e - 32] == hs_p2p_slot_[e] && pose_pos[hs_p2p_pose_[e - 32]] > pose_pos[hs_p2p_pose_[e]]) both |= 1;
     }
+    static_both_sides_ = both;
   }
   // envelope: every pose of a point chain reaches back to the chain's earliest pose
   int n_chains = 0;
-  for (int c : chain_of_point) n_chains = std::max(n_chains, c + 1);
+#pragma omp parallel for schedule(static) reduction(max : n_chains)
+  for (size_t i = 0; i < chain_of_point.size(); ++i) n_chains = std::max(n_chains, chain_of_point[i] + 1);
   std::vector<int> chain_min(n_chains, np);
-  for (size_t f = 0; f < in_p2p_pose_.size(); ++f) { int& m = chain_min[chain_of_point[in_p2p_point_[f]]]; m = std::min(m, pose_pos[in_p2p_pose_[f]]); }
-  for (size_t f = 0; f < in_ter_cur_.size(); ++f) { int& m = chain_min[chain_of_point[in_ter_cur_[f]]]; m = std::min(m, pose_pos[in_ter_motion_[f]]); }
+#pragma omp parallel for schedule(static)
+  for (int64_t f = 0; f < n_p2p; ++f) atomic_min(&chain_min[chain_of_point[in_p2p_point_[f]]], pose_pos[in_p2p_pose_[f]]);
+#pragma omp parallel for schedule(static)
+  for (int64_t f = 0; f < n_ter; ++f) atomic_min(&chain_min[chain_of_point[in_ter_cur_[f]]], pose_pos[in_ter_motion_[f]]);
   std::vector<int> first(np);
   std::iota(first.begin(), first.end(), 0);
-  for (size_t f = 0; f < in_p2p_pose_.size(); ++f) { int& r = first[pose_pos[in_p2p_pose_[f]]]; r = std::min(r, chain_min[chain_of_point[in_p2p_point_[f]]]); }
-  for (size_t f = 0; f < in_ter_cur_.size(); ++f) { int& r = first[pose_pos[in_ter_motion_[f]]]; r = std::min(r, chain_min[chain_of_point[in_ter_cur_[f]]]); }
+#pragma omp parallel for schedule(static)
+  for (int64_t f = 0; f < n_p2p; ++f) atomic_min(&first[pose_pos[in_p2p_pose_[f]]], chain_min[chain_of_point[in_p2p_point_[f]]]);
+#pragma omp parallel for schedule(static)
+  for (int64_t f = 0; f < n_ter; ++f) atomic_min(&first[pose_pos[in_ter_motion_[f]]], chain_min[chain_of_point[in_ter_cur_[f]]]);
   for (size_t f = 0; f < h_btw_a_.size(); ++f) {
     const int pa = pose_pos[h_btw_a_[f]], pb = pose_pos[h_btw_b_[f]];
     int& r = first[std::max(pa, pb)]; r = std::min(r, std::min(pa, pb));
@@ -386,8 +401,10 @@ inline void LmSolver::setup_band(const std::vector<int>& chain_of_point) {
     const int n_slots = (int)slot_point_.size();
     std::vector<int> slot_min(n_slots, 0x7fffffff), fwd_min(n_slots, 0x7fffffff);
     std::vector<char> link(n_slots, 0);
-    for (size_t f = 0; f < in_p2p_pose_.size(); ++f) { int& m = slot_min[point_slot_[in_p2p_point_[f]]]; m = std::min(m, pose_pos[in_p2p_pose_[f]]); }
-    for (size_t f = 0; f < in_ter_cur_.size(); ++f) { const int sc = point_slot_[in_ter_cur_[f]]; link[sc] = 1; slot_min[sc] = std::min(slot_min[sc], pose_pos[in_ter_motion_[f]]); }
+#pragma omp parallel for schedule(static)
+    for (int64_t f = 0; f < n_p2p; ++f) atomic_min(&slot_min[point_slot_[in_p2p_point_[f]]], pose_pos[in_p2p_pose_[f]]);
+#pragma omp parallel for schedule(static)
+    for (int64_t f = 0; f < n_ter; ++f) { const int sc = point_slot_[in_ter_cur_[f]]; link[sc] = 1; atomic_min(&slot_min[sc], pose_pos[in_ter_motion_[f]]); }
     for (int q = n_slots - 33; q >= 0; --q) if (link[q + 32]) fwd_min[q] = std::min(slot_min[q + 32], fwd_min[q + 32]);
     d_fwd_min_.upload(fwd_min, stream_);
   }
