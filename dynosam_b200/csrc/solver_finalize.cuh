@@ -18,12 +18,29 @@ inline void LmSolver::finalize() {
   auto lap = [&](int k) { lap_ms[k] = host_ms(lap_t); lap_t = std::chrono::steady_clock::now(); };
   // ---- chains from ternary links ----
   std::vector<int> in_link(npt, -1), out_link(npt, -1), degree(npt, 0);
-  for (int64_t f = 0; f < n_ter; ++f) {
-    const int c = in_ter_cur_[f], p = in_ter_prev_[f];
-    if (in_link[c] >= 0 || out_link[p] >= 0) throw ArgError("motion ternary factors must link points into simple chains (one predecessor, one successor per point)");
-    in_link[c] = (int)f; out_link[p] = (int)f;
+  {
+    bool twice = false;
+#pragma omp parallel for schedule(static) reduction(|| : twice)
+    for (int64_t f = 0; f < n_ter; ++f) {
+      const int was_in = __atomic_exchange_n(&in_link[in_ter_cur_[f]], (int)f, __ATOMIC_RELAXED);
+      const int was_out = __atomic_exchange_n(&out_link[in_ter_prev_[f]], (int)f, __ATOMIC_RELAXED);
+      if (was_in >= 0 || was_out >= 0) twice = true;
+    }
+    if (twice) throw ArgError("motion ternary factors must link points into simple chains (one predecessor, one successor per point)");
   }
-  for (int64_t f = 0; f < n_p2p; ++f) degree[in_p2p_point_[f]]++;
+  // rank[f]: position of a PoseToPoint factor among the factors of its point, in insertion order; degree = their count.
+  // Every piece of the point range scans the whole factor list and counts its own points only: the scan is a stream of
+  // 4-byte reads, the counters of a piece stay in its core's cache, and the result does not depend on the thread count.
+  std::vector<int> rank(n_p2p);
+  {
+    const int T = (int)std::max<int64_t>(1, std::min<int64_t>({16, (int64_t)omp_get_max_threads(), n_p2p / 65536 + 1}));
+#pragma omp parallel for schedule(static, 1)
+    for (int t = 0; t < T; ++t) {
+      const int lo = (int)((int64_t)npt * t / T), hi = (int)((int64_t)npt * (t + 1) / T);
+      const int32_t* pts = in_p2p_point_.data();
+      for (int64_t f = 0; f < n_p2p; ++f) { const int pt = pts[f]; if (pt >= lo && pt < hi) rank[f] = degree[pt]++; }
+    }
+  }
   struct Chain { int head, len, deg; };
   std::vector<Chain> chains;
   chains.reserve(npt);
@@ -46,7 +63,22 @@ inline void LmSolver::finalize() {
     }
     if (cyclic || visited != npt) throw ArgError("cycle in motion ternary links");
   }
-  std::stable_sort(chains.begin(), chains.end(), [](const Chain& a, const Chain& b) { return a.len != b.len ? a.len > b.len : a.deg > b.deg; });
+  {
+    // longest chains first, among equals the one with the most observations at a point first, else input order: two stable
+    // counting passes (degree, then length), the result a comparison sort on (len, deg) descending would give
+    auto sort_desc = [&](auto key) {
+      int top = 0;
+      for (const Chain& c : chains) top = std::max(top, key(c));
+      std::vector<int> start(top + 2, 0);
+      for (const Chain& c : chains) start[top - key(c) + 1]++;
+      for (int k = 0; k <= top; ++k) start[k + 1] += start[k];
+      std::vector<Chain> out(chains.size());
+      for (const Chain& c : chains) out[start[top - key(c)]++] = c;
+      chains.swap(out);
+    };
+    sort_desc([](const Chain& c) { return c.deg; });
+    sort_desc([](const Chain& c) { return c.len; });
+  }
 
   lap(0);
   const int n_chains = (int)chains.size();
@@ -91,7 +123,6 @@ inline void LmSolver::finalize() {
   }
   for (int r = 0; r < n_rows; ++r) row_base[r + 1] += row_base[r];
   const int n_entries = row_base[n_rows];
-  std::vector<int> fill(npt, 0);
   auto& p2p_pose = hs_p2p_pose_; p2p_pose.assign(n_entries, -1);
   auto& p2p_slot = hs_p2p_slot_; p2p_slot.assign(n_entries, -1);
   auto& p2p_group = hs_p2p_group_; p2p_group.assign(n_entries, 0);
@@ -99,8 +130,6 @@ inline void LmSolver::finalize() {
   auto& zy = hs_zy_; zy.assign(n_entries, 0.0);
   auto& zz = hs_zz_; zz.assign(n_entries, 0.0);
   p2p_entry_of_input_.assign(n_p2p, -1);
-  std::vector<int> rank(n_p2p);   // position of a factor among the factors of its point, in insertion order
-  for (int64_t f = 0; f < n_p2p; ++f) rank[f] = fill[in_p2p_point_[f]]++;
 #pragma omp parallel for schedule(static)
   for (int64_t f = 0; f < n_p2p; ++f) {
     const int pt = in_p2p_point_[f], slot = point_slot_[pt];
