@@ -122,6 +122,12 @@ class WorldMotionFormulation {
 
   HostGraph& graph() { return g_; }
   const HostGraph& graph() const { return g_; }
+  // room for a graph over about n_obs point observations (every observation is at most one point value, one PoseToPoint
+  // factor and one motion factor), so that the tables below do not rehash and the factor lists do not move while they grow
+  void reserve(size_t n_obs) {
+    g_.p2p.reserve(n_obs); g_.ternary.reserve(n_obs);
+    g_.values.points.reserve(n_obs); in_map_.reserve(n_obs); dynamic_in_map_.reserve(n_obs);
+  }
 
   void setInitialPose(const P3& T, FrameId k) { g_.values.poses[CameraPoseSymbol(k)] = T; }
   void setInitialPosePrior(const P3& T, FrameId k) { g_.add_prior(CameraPoseSymbol(k), T, noise_.initial_pose_prior); }
@@ -294,6 +300,15 @@ inline HostGraph construct_window_graph(const BackendParams& params, std::shared
   if (!(from < to)) throw std::runtime_error("constructGraph: from_frame must be < to_frame");
   if (from < map->first_frame() || to > map->last_frame()) throw std::runtime_error("constructGraph: window outside the map");
   WorldMotionFormulation fm(params, map);
+  {
+    size_t n_obs = 0;
+    for (FrameId f = from; f <= to; ++f) {
+      const Map::Frame* fr = map->frame(f);
+      n_obs += fr->static_tracklets.size();
+      for (const auto& kv : fr->object_tracklets) n_obs += kv.second.size();
+    }
+    fm.reserve(n_obs);
+  }
   for (FrameId f = from; f <= to; ++f) {
     const P3 T = map->frame(f)->T_world_camera;
     if (f == from) {

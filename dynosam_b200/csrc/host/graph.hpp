@@ -5,7 +5,9 @@
 // blocks with dense integer variable indices for the device solver.
 #pragma once
 #include <cstdint>
+#include <algorithm>
 #include <map>
+#include <unordered_map>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -39,11 +41,11 @@ struct BetweenFactorRec { Key a, b; P3 z; Noise noise; int32_t order; };
 struct PoseToPointRec { Key x, p; V3 z; int32_t noise_id; int32_t order; };
 struct MotionTernaryRec { Key prev, cur, motion; int32_t noise_id; int32_t order; };
 
-// gtsam::Values restricted to the two variable types on this path. std::map
-// iterates in ascending key order like gtsam::Values.
+// gtsam::Values restricted to the two variable types on this path. The poses sit in a std::map (ascending key order like
+// gtsam::Values); the points, two orders of magnitude more of them, in a hash table that flatten() puts into key order.
 struct Values {
   std::map<Key, P3> poses;
-  std::map<Key, V3> points;
+  std::unordered_map<Key, V3> points;
   bool exists(Key k) const { return is_pose_key(k) ? poses.count(k) != 0 : points.count(k) != 0; }
   void insert_pose(Key k, const P3& p) { if (!poses.emplace(k, p).second) throw std::runtime_error("ValuesKeyAlreadyExists"); }
   void insert_point(Key k, const V3& p) { if (!points.emplace(k, p).second) throw std::runtime_error("ValuesKeyAlreadyExists"); }
@@ -98,30 +100,52 @@ struct FlatGraph {
 // that has no value.
 inline FlatGraph flatten(const HostGraph& g) {
   FlatGraph f;
-  std::map<Key, int32_t> pose_index, point_index;
+  std::map<Key, int32_t> pose_index;
+  const size_t n_pose = g.values.poses.size(), n_point = g.values.points.size(), n_p2p = g.p2p.size(), n_ter = g.ternary.size();
+  f.pose_keys.reserve(n_pose); f.pose_Rt.reserve(12 * n_pose);
   for (const auto& kv : g.values.poses) {
     pose_index.emplace(kv.first, (int32_t)f.pose_keys.size());
     f.pose_keys.push_back(kv.first);
     double buf[12]; p3_store(kv.second, buf);
     f.pose_Rt.insert(f.pose_Rt.end(), buf, buf + 12);
   }
-  for (const auto& kv : g.values.points) {
-    point_index.emplace(kv.first, (int32_t)f.point_keys.size());
-    f.point_keys.push_back(kv.first);
-    f.point_xyz.push_back(kv.second.x); f.point_xyz.push_back(kv.second.y); f.point_xyz.push_back(kv.second.z);
+  // points in ascending key order; the index of a key is then a hash lookup
+  std::vector<std::pair<Key, const V3*>> sorted;
+  sorted.reserve(n_point);
+  for (const auto& kv : g.values.points) sorted.emplace_back(kv.first, &kv.second);
+  std::sort(sorted.begin(), sorted.end(), [](const std::pair<Key, const V3*>& a, const std::pair<Key, const V3*>& b) { return a.first < b.first; });
+  std::unordered_map<Key, int32_t> point_index;
+  point_index.reserve(2 * n_point);
+  f.point_keys.resize(n_point); f.point_xyz.resize(3 * n_point);
+  for (size_t i = 0; i < n_point; ++i) {
+    point_index.emplace(sorted[i].first, (int32_t)i);
+    f.point_keys[i] = sorted[i].first;
+    f.point_xyz[3 * i] = sorted[i].second->x; f.point_xyz[3 * i + 1] = sorted[i].second->y; f.point_xyz[3 * i + 2] = sorted[i].second->z;
   }
   auto pose_of = [&](Key k) { auto it = pose_index.find(k); if (it == pose_index.end()) throw std::out_of_range("ValuesKeyDoesNotExist: pose key " + std::to_string(k)); return it->second; };
   auto point_of = [&](Key k) { auto it = point_index.find(k); if (it == point_index.end()) throw std::out_of_range("ValuesKeyDoesNotExist: point key " + std::to_string(k)); return it->second; };
   double buf[12];
-  for (const PoseToPointRec& F : g.p2p) {
-    f.p2p_pose.push_back(pose_of(F.x)); f.p2p_point.push_back(point_of(F.p)); f.p2p_order.push_back(F.order);
-    f.p2p_z.push_back(F.z.x); f.p2p_z.push_back(F.z.y); f.p2p_z.push_back(F.z.z);
-    f.p2p_sigma.push_back(g.point_noise[F.noise_id].sigmas[0]); f.p2p_huber.push_back(g.point_noise[F.noise_id].huber_k);
+  f.p2p_pose.resize(n_p2p); f.p2p_point.resize(n_p2p); f.p2p_order.resize(n_p2p); f.p2p_z.resize(3 * n_p2p); f.p2p_sigma.resize(n_p2p); f.p2p_huber.resize(n_p2p);
+  {
+    Key last_pose = 0; int32_t last_pose_index = -1;   // the factors of one frame follow each other
+    for (size_t i = 0; i < n_p2p; ++i) {
+      const PoseToPointRec& F = g.p2p[i];
+      if (last_pose_index < 0 || F.x != last_pose) { last_pose_index = pose_of(F.x); last_pose = F.x; }
+      f.p2p_pose[i] = last_pose_index; f.p2p_point[i] = point_of(F.p); f.p2p_order[i] = F.order;
+      f.p2p_z[3 * i] = F.z.x; f.p2p_z[3 * i + 1] = F.z.y; f.p2p_z[3 * i + 2] = F.z.z;
+      f.p2p_sigma[i] = g.point_noise[F.noise_id].sigmas[0]; f.p2p_huber[i] = g.point_noise[F.noise_id].huber_k;
+    }
   }
-  for (const MotionTernaryRec& F : g.ternary) {
-    f.ter_prev.push_back(point_of(F.prev)); f.ter_cur.push_back(point_of(F.cur)); f.ter_motion.push_back(pose_of(F.motion));
-    f.ter_order.push_back(F.order);
-    f.ter_sigma.push_back(g.point_noise[F.noise_id].sigmas[0]); f.ter_huber.push_back(g.point_noise[F.noise_id].huber_k);
+  f.ter_prev.resize(n_ter); f.ter_cur.resize(n_ter); f.ter_motion.resize(n_ter); f.ter_order.resize(n_ter); f.ter_sigma.resize(n_ter); f.ter_huber.resize(n_ter);
+  {
+    Key last_pose = 0; int32_t last_pose_index = -1;
+    for (size_t i = 0; i < n_ter; ++i) {
+      const MotionTernaryRec& F = g.ternary[i];
+      if (last_pose_index < 0 || F.motion != last_pose) { last_pose_index = pose_of(F.motion); last_pose = F.motion; }
+      f.ter_prev[i] = point_of(F.prev); f.ter_cur[i] = point_of(F.cur); f.ter_motion[i] = last_pose_index;
+      f.ter_order[i] = F.order;
+      f.ter_sigma[i] = g.point_noise[F.noise_id].sigmas[0]; f.ter_huber[i] = g.point_noise[F.noise_id].huber_k;
+    }
   }
   for (const BetweenFactorRec& F : g.betweens) {
     f.btw_a.push_back(pose_of(F.a)); f.btw_b.push_back(pose_of(F.b)); f.btw_order.push_back(F.order);
