@@ -127,6 +127,7 @@ struct BandSystem {
   double* Linv = nullptr;          // [n_pad / 64][64 x 64] inverses of the diagonal blocks of the factor
   long long* prof = nullptr;       // optional [8] ns counters of the factorisation phases (verbose >= 3)
   const int* first64 = nullptr;    // [n_pad / 64] smallest first envelope column over each group of 64 rows
+  const int* row_start = nullptr;  // [n_pad] first envelope column of every row (storage coordinates): left of it the row is exactly zero, before and after the factorisation
   // Two-front (twisted) factorisation: a front is a band storage over a contiguous range of the time-ordered system that
   // is eliminated towards the separator in the middle. n stays the real dimension of the whole system, n_pad is the
   // number of rows of THIS storage.

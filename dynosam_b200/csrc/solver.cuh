@@ -390,7 +390,7 @@ class LmSolver {
   bool twisted_ = false;
   int split_m_ = 0, split_s_ = 0, chol_iters_ = 0, chol_iters1_ = 0, chol_iters2_ = 0;
   DevBuf<double> d_S2_, d_y2_, d_zb2_, d_Linv2_, d_rdiag2_, d_xt_, d_sep_;
-  DevBuf<int> d_first64B_;
+  DevBuf<int> d_first64B_, d_row_start_, d_row_startB_, d_first64F_, d_row_startF_;
   DevBuf<int> d_pose_pos_, d_pos_pose_, d_row_first_, d_first64_, d_fwd_min_;
   DevBuf<double> d_S_, d_y_, d_zb_, d_Linv_, d_rdiag_, d_G_, d_res_;
   DevBuf<long long> d_prof_;
