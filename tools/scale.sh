@@ -1,9 +1,9 @@
 #!/bin/bash
-# tools/scale.sh N workload... : sharded bench lines at N GPUs into gpurun_out/r1e_bench_<workload>_sharded<N>.json
+# tools/scale.sh N workload... : sharded bench lines at N GPUs into gpurun_out/$TAG_bench_<workload>_sharded<N>.json (TAG defaults to r1e)
 cd "$(dirname "$0")/.."
 N=$1; shift
 for w in "$@"; do
-  out=gpurun_out/r1e_bench_${w}_sharded${N}
+  out=gpurun_out/${TAG:-r1e}_bench_${w}_sharded${N}
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 2 --warmup 2 --workload $w --sharded > $out.json 2> $out.err
   python - <<PY
 import json
