@@ -86,8 +86,24 @@ struct Map {
     std::map<ObjectId, P3> motions;
     bool object_observed(ObjectId o) const { return object_tracklets.count(o) != 0; }
   };
+  // tracks by tracklet id: a flat index into a dense store (no node per track, no pointer chase per lookup)
+  struct TrackTable {
+    Track& operator[](TrackletId id) {
+      auto r = index.emplace((std::uint64_t)id, (int32_t)store.size());
+      if (r.second) store.emplace_back();
+      return store[*r.first];
+    }
+    const Track& at(TrackletId id) const {
+      const int32_t* i = index.find((std::uint64_t)id);
+      if (!i) throw std::out_of_range("unknown tracklet " + std::to_string((long long)id));
+      return store[*i];
+    }
+    size_t size() const { return store.size(); }
+    KeyMap<int32_t> index;
+    std::vector<Track> store;
+  };
   std::map<FrameId, Frame> frames;
-  std::unordered_map<TrackletId, Track> tracks;
+  TrackTable tracks;
 
   void update(const FrontendPacket& pk) {
     Frame& fr = frames[pk.frame];
@@ -166,30 +182,34 @@ class WorldMotionFormulation {
     const Map::Frame* fr_k1 = k > 0 ? map_->frame(k - 1) : nullptr;
     if (!fr_k || !fr_k1) throw std::runtime_error("updateDynamicObservations: frames k and k-1 must be in the map");
     std::map<ObjectId, std::set<FrameId>> affected;
+    // the sensor poses do not change while the points of this frame are added: one query per frame, not per point
+    const P3* X_k1_in_values = sensor_pose(k - 1);
+    const P3 X_k1_any = initial_or_linearized_sensor_pose(k - 1), X_k_any = initial_or_linearized_sensor_pose(k);
     for (const auto& obj_kv : fr_k->object_tracklets) {
       const ObjectId object = obj_kv.first;
       if (!map_->object_motion_expected(k, object)) continue;
       const std::vector<TrackletId>& seen_k = obj_kv.second;
       if (seen_k.size() < kMinNumberPoints || fr_k1->object_tracklets.at(object).size() < kMinNumberPoints) continue;
+      bool any = false;
       for (TrackletId id : seen_k) {
         const Map::Track& tr = map_->tracks.at(id);
         if ((int)tr.obs.size() < params_.min_dynamic_obs) continue;
-        if (!dynamic_in_map_.count(id)) {
+        if (!dynamic_in_map_.count((std::uint64_t)id)) {
           const FrameId first = tr.obs.front().first;
           if (k < first + 1) continue;  // cannot index backwards from the first observation
           // walk (k-1, k) pairs from k up to and including k (no backtrack => exactly one)
           const int idx = tr.index_of(k);
           const FrameId prev_seen = tr.obs[idx - 1].first;
           if (prev_seen + 1 != k) throw std::runtime_error("dynamic tracklet observations are not on consecutive frames");
-          const P3* X_k1 = sensor_pose(k - 1);
-          if (!X_k1) throw std::runtime_error("Failed cam pose query at frame k-1");
+          if (!X_k1_in_values) throw std::runtime_error("Failed cam pose query at frame k-1");
           // reference quirk (Formulation-impl.hpp:470-471): the k-1 pose also initialises the point at k
-          const P3 X_k = initial_or_linearized_sensor_pose(k - 1);
-          dynamicPointUpdate(tr, id, k, *X_k1, X_k, true, affected);
+          dynamicPointUpdate(tr, id, k, *X_k1_in_values, X_k1_any, true);
         } else {
-          dynamicPointUpdate(tr, id, k, initial_or_linearized_sensor_pose(k - 1), initial_or_linearized_sensor_pose(k), false, affected);
+          dynamicPointUpdate(tr, id, k, X_k1_any, X_k_any, false);
         }
+        any = true;
       }
+      if (any) { std::set<FrameId>& frames = affected[object]; frames.insert(k - 1); frames.insert(k); }   // every point update touches the object at k-1 and k
     }
     for (const auto& kv : affected) {
       if (kv.second.size() < 2) throw std::runtime_error("object affected on fewer than two frames");
@@ -207,24 +227,21 @@ class WorldMotionFormulation {
     return fr->T_world_camera;
   }
 
-  void dynamicPointUpdate(const Map::Track& tr, TrackletId id, FrameId k, const P3& X_k1, const P3& X_k, bool starting, std::map<ObjectId, std::set<FrameId>>& affected) {
+  void dynamicPointUpdate(const Map::Track& tr, TrackletId id, FrameId k, const P3& X_k1, const P3& X_k, bool starting) {
     const Key key_k1 = DynamicLandmarkSymbol(k - 1, id), key_k = DynamicLandmarkSymbol(k, id);
-    const ObjectId object = tr.object;
+    const int at_k = tr.index_of(k);   // observations are on consecutive frames here: k-1 is the one before
     if (starting) {
       if (g_.values.exists(key_k1)) throw std::runtime_error("dynamic point at k-1 already exists on its starting motion frame");
-      const V3 z1 = *tr.find(k - 1);
+      const V3 z1 = tr.obs[at_k - 1].second;
       g_.add_pose_to_point(CameraPoseSymbol(k - 1), key_k1, z1, noise_.dynamic_point_noise);
-      affected[object].insert(k - 1);
       g_.values.insert_point(key_k1, p3_apply(X_k1, z1));
     }
     if (!g_.values.exists(key_k1)) throw std::runtime_error("previous dynamic point missing (tracklet has a gap)");
-    const V3 z = *tr.find(k);
+    const V3 z = tr.obs[at_k].second;
     g_.add_pose_to_point(CameraPoseSymbol(k), key_k, z, noise_.dynamic_point_noise);
-    affected[object].insert(k);
     g_.values.insert_point(key_k, p3_apply(X_k, z));
-    g_.add_motion_ternary(key_k1, key_k, ObjectMotionSymbol(object, k), noise_.landmark_motion_noise);
-    affected[object].insert(k - 1);
-    dynamic_in_map_.insert(id);
+    g_.add_motion_ternary(key_k1, key_k, ObjectMotionSymbol(tr.object, k), noise_.landmark_motion_noise);
+    dynamic_in_map_.insert((std::uint64_t)id);
   }
 
   void objectUpdate(ObjectId object, FrameId f, bool has_motion_pair) {
@@ -253,8 +270,8 @@ class WorldMotionFormulation {
   NoiseModels noise_;
   std::shared_ptr<Map> map_;
   HostGraph g_;
-  std::unordered_set<Key> in_map_;               // is_other_values_in_map
-  std::unordered_set<TrackletId> dynamic_in_map_;  // is_dynamic_tracklet_in_map_
+  KeySet in_map_;               // is_other_values_in_map
+  KeySet dynamic_in_map_;       // is_dynamic_tracklet_in_map_ (by tracklet id)
 };
 
 // RGBDBackendModule::SlidingWindow (reference RGBDBackendModule.hpp:87-145)
