@@ -79,20 +79,24 @@ struct Map {
     const V3* find(FrameId f) const { const int i = index_of(f); return i < 0 ? nullptr : &obs[i].second; }
     bool seen_at(FrameId f) const { return index_of(f) >= 0; }
   };
+  // one observation of a frame: the tracklet, where its track sits in the table and which of the track's observations this is
+  // (so that the emission reaches the measurement without a hash lookup and a search per point)
+  struct Seen { TrackletId id; std::int32_t track; std::int32_t pos; };
   struct Frame {
     P3 T_world_camera;
-    std::vector<TrackletId> static_tracklets;                      // ascending id
-    std::map<ObjectId, std::vector<TrackletId>> object_tracklets;  // per object, ascending id
+    std::vector<Seen> static_tracklets;                      // ascending id
+    std::map<ObjectId, std::vector<Seen>> object_tracklets;  // per object, ascending id
     std::map<ObjectId, P3> motions;
     bool object_observed(ObjectId o) const { return object_tracklets.count(o) != 0; }
   };
   // tracks by tracklet id: a flat index into a dense store (no node per track, no pointer chase per lookup)
   struct TrackTable {
-    Track& operator[](TrackletId id) {
+    std::int32_t slot(TrackletId id) {   // position in `store`, a new empty track if the id is new
       auto r = index.emplace((std::uint64_t)id, (int32_t)store.size());
       if (r.second) store.emplace_back();
-      return store[*r.first];
+      return *r.first;
     }
+    Track& operator[](TrackletId id) { return store[slot(id)]; }
     const Track& at(TrackletId id) const {
       const int32_t* i = index.find((std::uint64_t)id);
       if (!i) throw std::out_of_range("unknown tracklet " + std::to_string((long long)id));
@@ -110,17 +114,20 @@ struct Map {
     fr.T_world_camera = pk.T_world_camera;
     fr.motions = pk.motions;
     for (const PointObs& o : pk.static_obs) {
-      Track& t = tracks[o.tracklet];
+      const std::int32_t ti = tracks.slot(o.tracklet);
+      Track& t = tracks.store[ti];
       t.object = 0; t.obs.emplace_back(pk.frame, o.z);
-      fr.static_tracklets.push_back(o.tracklet);
+      fr.static_tracklets.push_back({o.tracklet, ti, (std::int32_t)t.obs.size() - 1});
     }
     for (const PointObs& o : pk.dynamic_obs) {
-      Track& t = tracks[o.tracklet];
+      const std::int32_t ti = tracks.slot(o.tracklet);
+      Track& t = tracks.store[ti];
       t.object = o.object; t.obs.emplace_back(pk.frame, o.z);
-      fr.object_tracklets[o.object].push_back(o.tracklet);
+      fr.object_tracklets[o.object].push_back({o.tracklet, ti, (std::int32_t)t.obs.size() - 1});
     }
-    std::sort(fr.static_tracklets.begin(), fr.static_tracklets.end());
-    for (auto& kv : fr.object_tracklets) std::sort(kv.second.begin(), kv.second.end());
+    auto by_id = [](const Seen& a, const Seen& b) { return a.id < b.id; };
+    std::sort(fr.static_tracklets.begin(), fr.static_tracklets.end(), by_id);
+    for (auto& kv : fr.object_tracklets) std::sort(kv.second.begin(), kv.second.end(), by_id);
   }
   const Frame* frame(FrameId f) const { auto it = frames.find(f); return it == frames.end() ? nullptr : &it->second; }
   FrameId first_frame() const { return frames.begin()->first; }
@@ -160,15 +167,15 @@ class WorldMotionFormulation {
     const Map::Frame* fr = map_->frame(k);
     if (!fr) throw std::runtime_error("updateStaticObservations: unknown frame");
     const Key pose_key = CameraPoseSymbol(k);
-    for (TrackletId id : fr->static_tracklets) {
-      const Map::Track& tr = map_->tracks.at(id);
-      const Key point_key = StaticLandmarkSymbol(id);
+    for (const Map::Seen& seen : fr->static_tracklets) {
+      const Map::Track& tr = map_->tracks.store[seen.track];
+      const Key point_key = StaticLandmarkSymbol(seen.id);
       if (in_map_.count(point_key)) {
-        g_.add_pose_to_point(pose_key, point_key, *tr.find(k), noise_.static_point_noise);
+        g_.add_pose_to_point(pose_key, point_key, tr.obs[seen.pos].second, noise_.static_point_noise);
       } else {
         if ((int)tr.obs.size() < params_.min_static_obs) continue;
         // do_backtrack == false (RGBDBackendModule.cc:184-185, 303): only the current frame's factor
-        const V3 z = *tr.find(k);
+        const V3 z = tr.obs[seen.pos].second;
         g_.add_pose_to_point(pose_key, point_key, z, noise_.static_point_noise);
         g_.values.insert_point(point_key, p3_apply(fr->T_world_camera, z));
         in_map_.insert(point_key);
@@ -188,24 +195,25 @@ class WorldMotionFormulation {
     for (const auto& obj_kv : fr_k->object_tracklets) {
       const ObjectId object = obj_kv.first;
       if (!map_->object_motion_expected(k, object)) continue;
-      const std::vector<TrackletId>& seen_k = obj_kv.second;
+      const std::vector<Map::Seen>& seen_k = obj_kv.second;
       if (seen_k.size() < kMinNumberPoints || fr_k1->object_tracklets.at(object).size() < kMinNumberPoints) continue;
       bool any = false;
-      for (TrackletId id : seen_k) {
-        const Map::Track& tr = map_->tracks.at(id);
+      for (const Map::Seen& seen : seen_k) {
+        const TrackletId id = seen.id;
+        const Map::Track& tr = map_->tracks.store[seen.track];
         if ((int)tr.obs.size() < params_.min_dynamic_obs) continue;
+        const int idx = seen.pos;   // the observation at k
         if (!dynamic_in_map_.count((std::uint64_t)id)) {
           const FrameId first = tr.obs.front().first;
           if (k < first + 1) continue;  // cannot index backwards from the first observation
           // walk (k-1, k) pairs from k up to and including k (no backtrack => exactly one)
-          const int idx = tr.index_of(k);
           const FrameId prev_seen = tr.obs[idx - 1].first;
           if (prev_seen + 1 != k) throw std::runtime_error("dynamic tracklet observations are not on consecutive frames");
           if (!X_k1_in_values) throw std::runtime_error("Failed cam pose query at frame k-1");
           // reference quirk (Formulation-impl.hpp:470-471): the k-1 pose also initialises the point at k
-          dynamicPointUpdate(tr, id, k, *X_k1_in_values, X_k1_any, true);
+          dynamicPointUpdate(tr, id, idx, k, *X_k1_in_values, X_k1_any, true);
         } else {
-          dynamicPointUpdate(tr, id, k, X_k1_any, X_k_any, false);
+          dynamicPointUpdate(tr, id, idx, k, X_k1_any, X_k_any, false);
         }
         any = true;
       }
@@ -227,9 +235,9 @@ class WorldMotionFormulation {
     return fr->T_world_camera;
   }
 
-  void dynamicPointUpdate(const Map::Track& tr, TrackletId id, FrameId k, const P3& X_k1, const P3& X_k, bool starting) {
+  // at_k: which of the track's observations is the one at frame k (the one before it is at k-1 here)
+  void dynamicPointUpdate(const Map::Track& tr, TrackletId id, int at_k, FrameId k, const P3& X_k1, const P3& X_k, bool starting) {
     const Key key_k1 = DynamicLandmarkSymbol(k - 1, id), key_k = DynamicLandmarkSymbol(k, id);
-    const int at_k = tr.index_of(k);   // observations are on consecutive frames here: k-1 is the one before
     if (starting) {
       if (g_.values.exists(key_k1)) throw std::runtime_error("dynamic point at k-1 already exists on its starting motion frame");
       const V3 z1 = tr.obs[at_k - 1].second;
