@@ -99,6 +99,24 @@ struct FlatGraph {
 // throws std::out_of_range (the analogue of gtsam::ValuesKeyDoesNotExist,
 // reference src/backend/RGBDBackendModule.cc:378) when a factor names a key
 // that has no value.
+// ascending sort of 64-bit keys, least significant byte first; the bytes all keys share (the symbol character, unused
+// index bits) are skipped, so a window's point keys take three or four counting passes
+inline void sort_keys(std::vector<Key>& keys) {
+  if (keys.size() < 256) { std::sort(keys.begin(), keys.end()); return; }
+  Key all_or = 0, all_and = ~(Key)0;
+  for (Key k : keys) { all_or |= k; all_and &= k; }
+  const Key varying = all_or ^ all_and;
+  std::vector<Key> other(keys.size());
+  for (int byte = 0; byte < 8; ++byte) {
+    if (((varying >> (8 * byte)) & 0xff) == 0) continue;
+    size_t start[257] = {0};
+    for (Key k : keys) start[((k >> (8 * byte)) & 0xff) + 1]++;
+    for (int b = 0; b < 256; ++b) start[b + 1] += start[b];
+    for (Key k : keys) other[start[(k >> (8 * byte)) & 0xff]++] = k;
+    keys.swap(other);
+  }
+}
+
 inline FlatGraph flatten(const HostGraph& g) {
   FlatGraph f;
   std::map<Key, int32_t> pose_index;
@@ -113,7 +131,7 @@ inline FlatGraph flatten(const HostGraph& g) {
   // points in ascending key order; the index of a key is then a hash lookup
   f.point_keys.reserve(n_point);
   g.values.points.for_each([&](Key k, const V3&) { f.point_keys.push_back(k); });
-  std::sort(f.point_keys.begin(), f.point_keys.end());
+  sort_keys(f.point_keys);
   KeyMap<int32_t> point_index;
   point_index.reserve(n_point);
   f.point_xyz.resize(3 * n_point);
