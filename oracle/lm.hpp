@@ -11,6 +11,7 @@
 // fixed, lambdaUpper 1e5, lambdaLower 0, minModelFidelity 1e-3, lambda*I
 // damping, maxIterations 100, relative/absolute tol 1e-5, errorTol 0).
 #pragma once
+#include <chrono>
 #include <cstdio>
 
 #include "solver.hpp"
@@ -18,6 +19,7 @@
 namespace oracle {
 
 struct LMParams {
+  bool blocked_factorisation = true;   // false: the scalar skyline Cholesky (the two agree to round-off)
   double lambda_initial = 1e-5;
   double lambda_factor = 10.0;
   double lambda_upper = 1e5;
@@ -36,6 +38,8 @@ struct LMResult {
   double initial_error = 0, final_error = 0, lambda = 0;
   std::vector<double> error_per_iteration;  // error() after each outer iterate()
   std::vector<double> lambda_trace;         // lambda of every tryLambda solve
+  // wall-clock seconds per phase: linearise, assemble, point elimination, reduced factorisation, substitutions, error passes
+  double t_linearize = 0, t_assemble = 0, t_eliminate = 0, t_factor = 0, t_substitute = 0, t_error = 0;
 };
 
 inline void retract_all(const std::vector<Pose3>& poses, const std::vector<Vec3>& points,
@@ -91,8 +95,10 @@ inline LMResult levenberg_marquardt(FlatGraph& g, const LMParams& P, const int* 
   do {
     currentError = newError;
     // ---- LevenbergMarquardtOptimizer::iterate ----
-    graph_linearize(g, g.poses, g.points, lin);
-    if (!analysed) { solver.analyse(np, npt, lin, pose_order_hint); analysed = true; }
+    { const auto t0 = std::chrono::steady_clock::now();
+      graph_linearize(g, g.poses, g.points, lin);
+      R.t_linearize += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+    if (!analysed) { solver.analyse(np, npt, lin, pose_order_hint); solver.use_blocked = P.blocked_factorisation; analysed = true; }
     while (true) {
       // ---- tryLambda ----
       R.lambda_trace.push_back(lambda);
@@ -105,7 +111,9 @@ inline LMResult levenberg_marquardt(FlatGraph& g, const LMParams& P, const int* 
         const double linearizedCostChange = oldLinearizedError - newLinearizedError;
         if (linearizedCostChange >= 0) {
           retract_all(g.poses, g.points, dp, dpt, new_poses, new_points);
-          trialError = graph_error(g, new_poses, new_points);
+          { const auto t0 = std::chrono::steady_clock::now();
+            trialError = graph_error(g, new_poses, new_points);
+            R.t_error += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
           const double costChange = error - trialError;
           if (linearizedCostChange > std::numeric_limits<double>::epsilon() * oldLinearizedError) {
             modelFidelity = costChange / linearizedCostChange;
@@ -146,6 +154,7 @@ inline LMResult levenberg_marquardt(FlatGraph& g, const LMParams& P, const int* 
     if (R.iterations >= P.max_iterations || converged || !std::isfinite(currentError)) break;
   } while (true);
   R.final_error = error; R.lambda = lambda;
+  R.t_assemble = solver.t_assemble; R.t_eliminate = solver.t_eliminate; R.t_factor = solver.t_factor; R.t_substitute = solver.t_substitute;
   return R;
 }
 

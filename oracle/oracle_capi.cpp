@@ -109,10 +109,13 @@ void oracle_graph_linearize(oracle_graph* h, double* p2p_Apose, double* p2p_Apoi
 }
 
 // One exact damped solve at the current values: d = (A^T A + lambda I)^-1 A^T b. Returns 1 on success.
+static int g_blocked = 1;
+void oracle_set_blocked(int32_t on) { g_blocked = on; }   // factorisation used by oracle_solve_once (oracle_lm takes it in params[10])
 int32_t oracle_solve_once(oracle_graph* h, double lambda, const int32_t* pose_order_hint, double* d_pose, double* d_point) {
   std::vector<LinFactor> lin;
   graph_linearize(h->g, h->g.poses, h->g.points, lin);
   SchurSolver s;
+  s.use_blocked = g_blocked != 0;
   s.analyse((int)h->g.poses.size(), (int)h->g.points.size(), lin, pose_order_hint);
   std::vector<double> dp, dpt;
   if (!s.solve(lin, lambda, dp, dpt)) return 0;
@@ -123,15 +126,19 @@ int32_t oracle_solve_once(oracle_graph* h, double lambda, const int32_t* pose_or
 
 // params: [lambda_initial, lambda_factor, lambda_upper, lambda_lower, min_model_fidelity,
 //          max_iterations, relative_error_tol, absolute_error_tol, error_tol, verbose]
-// out_stats: [iterations, inner_iterations, initial_error, final_error, lambda, n_error_trace]
+//          [10] (optional, read when params[10] is given as n_params > 10) blocked factorisation on/off
+// out_stats: [iterations, inner_iterations, initial_error, final_error, lambda, n_error_trace,
+//             t_linearize, t_assemble, t_eliminate, t_factor, t_substitute, t_error]   (16 slots)
 void oracle_lm(oracle_graph* h, const double* params, const int32_t* pose_order_hint, double* out_stats, double* err_trace, int32_t cap) {
   LMParams P;
   P.lambda_initial = params[0]; P.lambda_factor = params[1]; P.lambda_upper = params[2]; P.lambda_lower = params[3];
   P.min_model_fidelity = params[4]; P.max_iterations = (int)params[5]; P.relative_error_tol = params[6];
   P.absolute_error_tol = params[7]; P.error_tol = params[8]; P.verbose = (int)params[9];
+  P.blocked_factorisation = params[10] != 0.0;
   LMResult R = levenberg_marquardt(h->g, P, pose_order_hint);
   out_stats[0] = R.iterations; out_stats[1] = R.inner_iterations; out_stats[2] = R.initial_error;
   out_stats[3] = R.final_error; out_stats[4] = R.lambda; out_stats[5] = (double)R.error_per_iteration.size();
+  out_stats[6] = R.t_linearize; out_stats[7] = R.t_assemble; out_stats[8] = R.t_eliminate; out_stats[9] = R.t_factor; out_stats[10] = R.t_substitute; out_stats[11] = R.t_error;
   for (int i = 0; i < cap && i < (int)R.error_per_iteration.size(); ++i) err_trace[i] = R.error_per_iteration[i];
 }
 

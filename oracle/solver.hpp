@@ -12,6 +12,7 @@
 // analogue of IndeterminantLinearSystemException (a failed lambda trial).
 #pragma once
 #include <algorithm>
+#include <chrono>
 #include <numeric>
 
 #include "graph.hpp"
@@ -125,7 +126,24 @@ struct SchurSolver {
     S.resize(row_ptr.back());
     w_blk.resize(18 * (size_t)w_pose.size()); pp_blk.resize(9 * (size_t)pp_other.size());
     V.resize(9 * (size_t)npt); gpt.resize(3 * (size_t)npt); gp.resize(6 * (size_t)np);
+    // variable -> (factor, slot) incidences in factor order: assemble() gives every variable's rows to one thread
+    inc_ptr.assign((size_t)np + npt + 1, 0);
+    for (const LinFactor& L : lin) for (int a = 0; a < L.nvar; ++a) inc_ptr[L.var[a] + 1]++;
+    for (size_t v = 0; v < (size_t)np + npt; ++v) inc_ptr[v + 1] += inc_ptr[v];
+    inc_fac.resize(inc_ptr.back()); inc_slot.resize(inc_ptr.back());
+    { std::vector<int64_t> fill(inc_ptr.begin(), inc_ptr.end() - 1);
+      for (size_t f = 0; f < lin.size(); ++f) for (int a = 0; a < lin[f].nvar; ++a) { const int64_t at = fill[lin[f].var[a]]++; inc_fac[at] = (int)f; inc_slot[at] = (unsigned char)a; } }
+    // pose position range of every cluster (eliminate_points hands out the reduced system by row ranges)
+    cluster_lo.assign(nc, np); cluster_hi.assign(nc, -1);
+    for (int c = 0; c < nc; ++c)
+      for (int k = cluster_ptr[c]; k < cluster_ptr[c + 1]; ++k)
+        for (int q = w_ptr[cluster_pts[k]]; q < w_ptr[cluster_pts[k] + 1]; ++q) {
+          cluster_lo[c] = std::min(cluster_lo[c], pos_of_pose[w_pose[q]]); cluster_hi[c] = std::max(cluster_hi[c], pos_of_pose[w_pose[q]]);
+        }
   }
+  std::vector<int64_t> inc_ptr;
+  std::vector<int> inc_fac, cluster_lo, cluster_hi;
+  std::vector<unsigned char> inc_slot;
 
   inline double& Sat(int row, int col) { return S[row_ptr[row] + (col - row_first[row])]; }
 
@@ -134,9 +152,15 @@ struct SchurSolver {
     std::fill(S.begin(), S.end(), 0.0); std::fill(gp.begin(), gp.end(), 0.0);
     std::fill(V.begin(), V.end(), 0.0); std::fill(gpt.begin(), gpt.end(), 0.0);
     std::fill(w_blk.begin(), w_blk.end(), 0.0); std::fill(pp_blk.begin(), pp_blk.end(), 0.0);
-    for (const LinFactor& L : lin) {
-      for (int a = 0; a < L.nvar; ++a) {
-        const int va = L.var[a], da = L.vdim[a];
+    // every entry below is owned by the row variable va (its gradient, its diagonal block, its W / point-point blocks,
+    // its row of the reduced system): one thread per variable, incidences in factor order => deterministic sums
+    const int64_t nvar_total = (int64_t)np + npt;
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t va64 = 0; va64 < nvar_total; ++va64) {
+      const int va = (int)va64;
+      for (int64_t at = inc_ptr[va]; at < inc_ptr[va + 1]; ++at) {
+        const LinFactor& L = lin[inc_fac[at]];
+        const int a = inc_slot[at], da = L.vdim[a];
         // gradient
         for (int i = 0; i < da; ++i) {
           double s = 0;
@@ -207,6 +231,7 @@ struct SchurSolver {
     const int nc = (int)cluster_ptr.size() - 1;
     Minv.resize(nc);
     bool ok = true;
+    // phase 1: dense inverse of every cluster's point block
 #pragma omp parallel for schedule(dynamic, 64)
     for (int c = 0; c < nc; ++c) {
       const int n = cluster_ptr[c + 1] - cluster_ptr[c], N = 3 * n;
@@ -227,17 +252,35 @@ struct SchurSolver {
       if (!dense_spd_inverse(M, N, tmp)) {
 #pragma omp atomic write
         ok = false;
-        continue;
       }
-      // S -= W^T Minv W ; gp -= W^T Minv gpt
+    }
+    if (!ok) return false;
+    // phase 2: S -= W^T Minv W ; gp -= W^T Minv gpt. The rows of the reduced system are cut into ranges of pose
+    // positions; a range is one task that walks the clusters reaching into it (in cluster order) and writes only its
+    // own rows: no atomics, and sums that do not depend on the number of threads.
+    const int kRange = 8;
+    const int nrange = (np + kRange - 1) / kRange;
+    std::vector<std::vector<int>> range_clusters(nrange);
+    for (int c = 0; c < nc; ++c)
+      if (cluster_hi[c] >= 0) for (int rg = cluster_lo[c] / kRange; rg <= cluster_hi[c] / kRange; ++rg) range_clusters[rg].push_back(c);
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int rg = 0; rg < nrange; ++rg) {
+      const int p_lo = rg * kRange, p_hi = std::min(np, p_lo + kRange);
+      for (int c : range_clusters[rg]) {
+      const int n = cluster_ptr[c + 1] - cluster_ptr[c], N = 3 * n;
+      const std::vector<double>& M = Minv[c];
       for (int li = 0; li < n; ++li) {
         const int i = cluster_pts[cluster_ptr[c] + li];
+        bool mine = false;
+        for (int ka = w_ptr[i]; ka < w_ptr[i + 1]; ++ka) { const int pa = pos_of_pose[w_pose[ka]]; if (pa >= p_lo && pa < p_hi) mine = true; }
+        if (!mine) continue;
         for (int lj = 0; lj < n; ++lj) {
           const int j = cluster_pts[cluster_ptr[c] + lj];
           double Mij[9];
           for (int r = 0; r < 3; ++r) for (int q = 0; q < 3; ++q) Mij[3 * r + q] = M[(3 * li + r) * N + 3 * lj + q];
           for (int ka = w_ptr[i]; ka < w_ptr[i + 1]; ++ka) {
             const int pa = pos_of_pose[w_pose[ka]];
+            if (pa < p_lo || pa >= p_hi) continue;
             const double* Wa = &w_blk[18 * (size_t)ka];  // 3x6
             double T[18];                                // Wa^T Mij : 6x3
             for (int r = 0; r < 6; ++r) for (int q = 0; q < 3; ++q) {
@@ -248,7 +291,6 @@ struct SchurSolver {
             for (int r = 0; r < 6; ++r) {
               double s = 0;
               for (int q = 0; q < 3; ++q) s += T[r * 3 + q] * gpt[3 * (size_t)j + q];
-#pragma omp atomic
               gp[6 * pa + r] -= s;
             }
             for (int kb = w_ptr[j]; kb < w_ptr[j + 1]; ++kb) {
@@ -259,15 +301,15 @@ struct SchurSolver {
                 if (pa == pb && q > r) continue;
                 double s = 0;
                 for (int k = 0; k < 3; ++k) s += T[r * 3 + k] * Wb[k * 6 + q];
-#pragma omp atomic
                 Sat(6 * pa + r, 6 * pb + q) -= s;
               }
             }
           }
         }
       }
+      }
     }
-    return ok;
+    return true;
   }
 
   // skyline Cholesky, in place (lower, row-wise)
@@ -292,6 +334,124 @@ struct SchurSolver {
     return true;
   }
 
+  // ---- blocked, OpenMP-parallel skyline Cholesky ------------------------------------------------------------
+  // Same factor as factor_reduced() up to the order of the floating-point sums; this is the CPU arm that is TIMED as
+  // the baseline (bench.py cpu_baseline / --impl reference) and the one the full-size parity tests run, because the
+  // scalar row-by-row version above is serial.  Right-looking over panels of kNB columns: the panel's diagonal block is
+  // factored by one thread, the rows below it are solved against it in parallel (each row is its own task), the panel
+  // rows are packed into a dense (rows x kNB) array, and the trailing update A[i, c] -= P_i . P_c runs in parallel
+  // over row strips with a 4 x 4 register tile.  Every row is written by exactly one thread per phase, so the result
+  // does not depend on the number of threads.
+  static constexpr int kNB = 48;
+  double t_factor_diag = 0, t_factor_trsm = 0, t_factor_update = 0;
+  double t_assemble = 0, t_eliminate = 0, t_factor = 0, t_substitute = 0;   // seconds, accumulated over solve() calls
+
+  // C[q][0..15] = sum_k A[q][k] * Bt[k][0..15] for four rows q: the inner loop over the 16 columns is unit stride in Bt
+  // (the panel packed column-major), so the compiler turns it into broadcast-FMA on 256/512-bit vectors.
+  __attribute__((target_clones("avx512f", "avx2", "default")))
+  static void tile4x16(const double* a0, const double* a1, const double* a2, const double* a3, const double* bt, size_t ldb, int k, double* out /*4 x 16*/) {
+    double s0[16] = {0}, s1[16] = {0}, s2[16] = {0}, s3[16] = {0};
+    for (int m = 0; m < k; ++m) {
+      const double* b = bt + (size_t)m * ldb;
+      const double x0 = a0[m], x1 = a1[m], x2 = a2[m], x3 = a3[m];
+#pragma GCC ivdep
+      for (int j = 0; j < 16; ++j) { s0[j] += x0 * b[j]; s1[j] += x1 * b[j]; s2[j] += x2 * b[j]; s3[j] += x3 * b[j]; }
+    }
+    for (int j = 0; j < 16; ++j) { out[j] = s0[j]; out[16 + j] = s1[j]; out[32 + j] = s2[j]; out[48 + j] = s3[j]; }
+  }
+
+  bool factor_reduced_blocked() {
+    const int n = 6 * np;
+    if (n == 0) return true;
+    // last[c]: last row whose envelope reaches column c (prefix maximum), so a panel knows how far down it acts
+    std::vector<int> last(n, 0);
+    for (int i = 0; i < n; ++i) last[row_first[i]] = std::max(last[row_first[i]], i);
+    for (int c = 1; c < n; ++c) last[c] = std::max(last[c], last[c - 1]);
+    std::vector<double> Pt;  // the same, column-major (padded to 16 rows)
+    std::vector<double> P;   // packed panel rows, [row - i_begin][kNB], zero where a row starts right of a column
+    bool ok = true;
+    for (int j0 = 0; j0 < n && ok; j0 += kNB) {
+      const int j1 = std::min(n, j0 + kNB), nb = j1 - j0;
+      auto tick = std::chrono::steady_clock::now();
+      auto lap = [&](double& acc) { const auto now = std::chrono::steady_clock::now(); acc += std::chrono::duration<double>(now - tick).count(); tick = now; };
+      // diagonal block: rows j0..j1-1, columns j0..row (all inside the envelope or structurally zero)
+      for (int i = j0; i < j1; ++i) {
+        const int fi = row_first[i];
+        double* Li = &S[row_ptr[i]] - fi;
+        for (int j = std::max(j0, fi); j < i; ++j) {
+          const int fj = row_first[j];
+          const double* Lj = &S[row_ptr[j]] - fj;
+          double s = Li[j];
+          for (int k = std::max({j0, fi, fj}); k < j; ++k) s -= Li[k] * Lj[k];
+          Li[j] = s / Lj[j];
+        }
+        double d = Li[i];
+        for (int k = std::max(j0, fi); k < i; ++k) d -= Li[k] * Li[k];
+        if (!(d > 0)) { ok = false; break; }
+        Li[i] = std::sqrt(d);
+      }
+      if (!ok) break;
+      lap(t_factor_diag);
+      const int i_begin = j1, i_end = last[j1 - 1] + 1;   // rows below the panel that reach into it
+      if (i_end <= i_begin) continue;
+      const int nr = i_end - i_begin;
+      P.assign((size_t)nr * kNB, 0.0);
+      // panel solve L_iJ = A_iJ L_JJ^-T, row by row in parallel, and packing
+#pragma omp parallel for schedule(static)
+      for (int i = i_begin; i < i_end; ++i) {
+        const int fi = row_first[i];
+        if (fi >= j1) continue;
+        double* Li = &S[row_ptr[i]] - fi;
+        double* Pi = &P[(size_t)(i - i_begin) * kNB];
+        for (int j = std::max(j0, fi); j < j1; ++j) {
+          const int fj = row_first[j];
+          const double* Lj = &S[row_ptr[j]] - fj;
+          double s = Li[j];
+          for (int k = std::max({j0, fi, fj}); k < j; ++k) s -= Li[k] * Lj[k];
+          Li[j] = s / Lj[j];
+          Pi[j - j0] = Li[j];
+        }
+      }
+      lap(t_factor_trsm);
+      // trailing update: strips of 4 rows against 16 columns at a time; a row never writes left of its envelope
+      const size_t ldb = ((size_t)nr + 15) / 16 * 16;
+      Pt.assign((size_t)kNB * ldb, 0.0);
+#pragma omp parallel for schedule(static)
+      for (int r = 0; r < nr; ++r) for (int m = 0; m < nb; ++m) Pt[(size_t)m * ldb + r] = P[(size_t)r * kNB + m];
+      const int nstrip = (nr + 3) / 4;
+#pragma omp parallel for schedule(dynamic, 4)
+      for (int st = nstrip - 1; st >= 0; --st) {
+        const int r0 = st * 4;
+        const double* a[4];
+        int fmin = n;
+        bool any = false;
+        for (int q = 0; q < 4; ++q) {
+          const int r = std::min(r0 + q, nr - 1);
+          a[q] = &P[(size_t)r * kNB];
+          const int fi = row_first[i_begin + r];
+          if (fi < j1) any = true;
+          fmin = std::min(fmin, fi);
+        }
+        if (!any) continue;
+        const int c_lo = std::max(0, fmin - i_begin) / 16 * 16;
+        for (int c0 = c_lo; c0 <= r0 + 3; c0 += 16) {
+          double out[64];
+          tile4x16(a[0], a[1], a[2], a[3], &Pt[c0], ldb, nb, out);
+          for (int q = 0; q < 4 && r0 + q < nr; ++q) {
+            const int i = i_begin + r0 + q, fi = row_first[i];
+            double* Li = &S[row_ptr[i]] - fi;
+            const int t_lo = std::max(0, fi - (i_begin + c0)), t_hi = std::min(16, i - (i_begin + c0) + 1);
+            for (int t = t_lo; t < t_hi; ++t) Li[i_begin + c0 + t] -= out[16 * q + t];
+          }
+        }
+      }
+      lap(t_factor_update);
+    }
+    return ok;
+  }
+
+  bool use_blocked = true;   // oracle_set_blocked(0) selects the scalar factorisation (tests compare the two)
+
   void solve_reduced(std::vector<double>& x) const {  // x: rhs in, solution out (permuted scalar order)
     const int n = 6 * np;
     for (int i = 0; i < n; ++i) {
@@ -310,11 +470,17 @@ struct SchurSolver {
 
   // Full solve. d_pose: 6*np in natural pose order, d_point: 3*npt.
   bool solve(const std::vector<LinFactor>& lin, double lambda, std::vector<double>& d_pose, std::vector<double>& d_point) {
+    auto tick = std::chrono::steady_clock::now();
+    auto lap = [&](double& acc) { const auto now = std::chrono::steady_clock::now(); acc += std::chrono::duration<double>(now - tick).count(); tick = now; };
     assemble(lin, lambda);
+    lap(t_assemble);
     if (!eliminate_points()) return false;
-    if (!factor_reduced()) return false;
+    lap(t_eliminate);
+    if (!(use_blocked ? factor_reduced_blocked() : factor_reduced())) return false;
+    lap(t_factor);
     std::vector<double> x(gp);
     solve_reduced(x);
+    lap(t_substitute);
     d_pose.resize(6 * (size_t)np); d_point.resize(3 * (size_t)npt);
     for (int p = 0; p < np; ++p) for (int i = 0; i < 6; ++i) d_pose[6 * (size_t)p + i] = x[6 * (size_t)pos_of_pose[p] + i];
     const int nc = (int)cluster_ptr.size() - 1;

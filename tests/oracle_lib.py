@@ -48,6 +48,7 @@ def lib():
         _lib.oracle_solve_once.restype = C.c_int32
         _lib.oracle_solve_once.argtypes = [C.c_void_p, C.c_double, _ip, _dp, _dp]
         _lib.oracle_lm.argtypes = [C.c_void_p, _dp, _ip, _dp, _dp, C.c_int32]
+        _lib.oracle_set_blocked.argtypes = [C.c_int32]
         for name, n in [("oracle_se3_expmap", 2), ("oracle_se3_logmap", 2), ("oracle_se3_logmap_derivative", 2), ("oracle_se3_compose", 3),
                         ("oracle_se3_inverse", 2), ("oracle_se3_retract", 3), ("oracle_between_error", 6), ("oracle_prior_error", 4),
                         ("oracle_p2p_error", 6), ("oracle_ternary_error", 7)]:
@@ -158,24 +159,27 @@ class OracleGraph:
         lib().oracle_graph_linearize(self._h, *[_p(v) for v in out.values()])
         return out
 
-    def solve_once(self, lam):
+    def solve_once(self, lam, blocked=True):
+        lib().oracle_set_blocked(1 if blocked else 0)
         dp, dpt = np.zeros((self.n_pose, 6)), np.zeros((self.n_point, 3))
         hint = None if self.order_hint is None else _i32(self.order_hint)
         ok = lib().oracle_solve_once(self._h, lam, _i(hint), _p(dp), _p(dpt))
         return bool(ok), dp, dpt
 
     def optimize(self, max_iterations=100, relative_error_tol=1e-5, absolute_error_tol=1e-5, lambda_initial=1e-5, lambda_factor=10.0,
-                 lambda_upper=1e5, lambda_lower=0.0, min_model_fidelity=1e-3, error_tol=0.0, verbose=0):
+                 lambda_upper=1e5, lambda_lower=0.0, min_model_fidelity=1e-3, error_tol=0.0, verbose=0, blocked=True):
+        """blocked: the OpenMP-parallel blocked skyline Cholesky (default; the timed CPU arm) or the scalar one."""
         params = _f64([lambda_initial, lambda_factor, lambda_upper, lambda_lower, min_model_fidelity, max_iterations,
-                       relative_error_tol, absolute_error_tol, error_tol, verbose])
-        stats = np.zeros(8)
+                       relative_error_tol, absolute_error_tol, error_tol, verbose, 1.0 if blocked else 0.0])
+        stats = np.zeros(16)
         cap = max_iterations + 2
         trace = np.zeros(cap)
         hint = None if self.order_hint is None else _i32(self.order_hint)
         lib().oracle_lm(self._h, _p(params), _i(hint), _p(stats), _p(trace), cap)
         n = int(stats[5])
         return {"iterations": int(stats[0]), "inner_iterations": int(stats[1]), "initial_error": stats[2], "final_error": stats[3],
-                "lambda": stats[4], "error_trace": [stats[2]] + trace[:min(n, cap)].tolist()}
+                "lambda": stats[4], "error_trace": [stats[2]] + trace[:min(n, cap)].tolist(),
+                "phase_s": dict(zip(("linearize", "assemble", "eliminate_points", "factor_reduced", "substitute", "error"), stats[6:12].tolist()))}
 
     def __del__(self):
         if getattr(self, "_h", None):

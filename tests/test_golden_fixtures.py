@@ -50,7 +50,9 @@ def test_oracle_lm_matches_fixture(name):
     r = ora.optimize(max_iterations=t["budget"], relative_error_tol=0.0, absolute_error_tol=0.0)
     got, want = np.array(r["error_trace"]), np.array(t["error_trace"])
     assert len(got) == len(want)
-    assert np.all(np.abs(got - want) <= 1e-9 * np.abs(want) + FLOOR)
+    # 1e-8: the noise-free simulator scene sits on the Huber kink and amplifies the round-off of a different summation
+    # order (blocked / scalar factorisation, thread-parallel assembly) to ~2e-9; north_star's bound is 1e-6
+    assert np.all(np.abs(got - want) <= 1e-8 * np.abs(want) + FLOOR)
     if want[-1] > FLOOR:
         assert (r["iterations"], r["inner_iterations"]) == (t["iterations"], t["inner_iterations"])
     pose, pt = ora.values()

@@ -113,3 +113,22 @@ def test_lm_error_is_monotone_and_lambda_follows_the_schedule():
     # every accepted step divides lambda by 10, every rejected one multiplies it by 10
     rejected = r["inner_iterations"] - r["iterations"]
     assert r["lambda"] == pytest.approx(1e-5 * 10.0 ** (rejected - r["iterations"]), rel=1e-9)
+
+
+def test_blocked_factorisation_matches_scalar():
+    """The OpenMP-parallel blocked skyline Cholesky (the timed CPU arm) against the scalar row-by-row one: same
+    damped step to round-off, same LM trajectory, on a scene with a real band."""
+    import scenes
+    g = scenes.medium_noisy().full_batch_graph()
+    ora = OracleGraph.from_graph(g)
+    for lam in (1e-5, 1.0):
+        ok_b, dp_b, dpt_b = ora.solve_once(lam, blocked=True)
+        ok_s, dp_s, dpt_s = ora.solve_once(lam, blocked=False)
+        assert ok_b and ok_s
+        assert np.max(np.abs(dp_b - dp_s)) <= 1e-9 * np.max(np.abs(dp_s))
+        assert np.max(np.abs(dpt_b - dpt_s)) <= 1e-9 * np.max(np.abs(dpt_s))
+    a = OracleGraph.from_graph(g).optimize(max_iterations=3, relative_error_tol=0.0, absolute_error_tol=0.0, blocked=True)
+    b = OracleGraph.from_graph(g).optimize(max_iterations=3, relative_error_tol=0.0, absolute_error_tol=0.0, blocked=False)
+    assert (a["iterations"], a["inner_iterations"]) == (b["iterations"], b["inner_iterations"])
+    assert np.allclose(a["error_trace"], b["error_trace"], rtol=1e-9, atol=0)
+    assert a["phase_s"]["factor_reduced"] > 0
