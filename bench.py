@@ -45,10 +45,13 @@ WORKLOAD_NAMES = {
     "cfg2": "OMD swinging_4_unconstrained-shaped synthetic scene (4 rigid objects, 500 frames, ~200k measurements), full batch",
     "cfg5": "large synthetic city scene (10k frames, 100 objects, ~47M factors), full batch",
 }
-# the CPU arm's bounded sample: a slice of cfg3's shape (6 objects are visible at a time in cfg3)
-CPU_SAMPLE = dict(n_frames=80, n_objects=6, static_per_frame=900, dynamic_per_object=100, object_span=0, seed=1003)
-CPU_SAMPLES = {"cfg5": dict(n_frames=40, n_objects=3, static_per_frame=2500, dynamic_per_object=417, object_span=0, seed=1005)}
-CPU_SAMPLE_ITERS = 2
+# The CPU arm (cpu_baseline, --impl reference) runs the FULL workload for cfg2 / cfg3: one step = CPU_ITERS LM iterations of
+# the restated oracle (OpenMP: linearise, owner-parallel assembly, point elimination, blocked skyline Cholesky) from the
+# front-end values. cfg5 (47 M factors) needs ~50 GB for the oracle's per-factor Jacobian blocks, so its CPU arm stays a
+# slice of the same shape scaled by factor count, and says so.
+CPU_SLICES = {"cfg5": dict(n_frames=40, n_objects=3, static_per_frame=2500, dynamic_per_object=417, object_span=0, seed=1005)}
+CPU_ITERS = 2
+CPU_TIME_BUDGET_S = 240.0   # --impl reference: the timed steps are cut short when K steps would not fit in this
 # algorithmic bytes of one fused linearise -> normal-equations pass
 C_P2P, C_TER, C_BTW, C_PRI, C_POSE, C_POINT = 176, 372, 392, 100, 312, 96
 
@@ -116,43 +119,73 @@ def lm_params(device=0):
     return p
 
 
-def cpu_oracle_run(steps, warmup, workload="cfg3"):
-    """The restated CPU oracle (GTSAM itself is not installable offline) on a bounded sample."""
+def common_config(workload, g):
+    """The part of `config` both arms print: same workload, same graph."""
+    return {"workload": WORKLOAD_NAMES[workload], "formulation": "MotionInWorld (world-centric; the fork has no hybrid formulation)",
+            "factors": g.n_factors, "measurements": g.n_p2p, "poses": g.n_pose, "points": g.n_point}
+
+
+def cpu_oracle_run(steps, warmup, workload="cfg3", g=None, budget_s=None):
+    """The restated CPU oracle (GTSAM itself is not installable offline). One step = CPU_ITERS LM iterations from the
+    front-end values; the oracle's copy of the graph is made once and its values are restored between steps.
+    Returns (graph the oracle ran, per-step seconds, LM iterations, per-phase seconds, scale to the full workload)."""
     import dynosam_b200 as d
     from oracle_lib import OracleGraph
-    scene = d.Scene.synthetic(**CPU_SAMPLES.get(workload, CPU_SAMPLE))
-    g = scene.full_batch_graph()
-    times, iters = [], 0
+    scale = 1.0
+    if workload in CPU_SLICES:
+        full = g if g is not None else build_graph(WORKLOADS[workload])[1]
+        g = d.Scene.synthetic(**CPU_SLICES[workload]).full_batch_graph()
+        scale = full.n_factors / g.n_factors
+    elif g is None:
+        _, g = build_graph(WORKLOADS[workload])
+    ora = OracleGraph.from_graph(g)
+    times, iters, phases = [], 0, {}
+    t_begin = time.perf_counter()
     for s in range(warmup + steps):
-        ora = OracleGraph.from_graph(g)
+        ora.set_values(g.pose_Rt, g.point_xyz)
         t0 = time.perf_counter()
-        r = ora.optimize(max_iterations=CPU_SAMPLE_ITERS, relative_error_tol=0.0, absolute_error_tol=0.0)
+        r = ora.optimize(max_iterations=CPU_ITERS, relative_error_tol=0.0, absolute_error_tol=0.0)
         dt = time.perf_counter() - t0
         if s >= warmup:
             times.append(dt); iters += r["iterations"]
-    return g, times, iters
+            for k, v in r["phase_s"].items():
+                phases[k] = phases.get(k, 0.0) + v
+        done = s + 1
+        if budget_s is not None and done >= warmup + 1 and done < warmup + steps:
+            per = (time.perf_counter() - t_begin) / done
+            if (time.perf_counter() - t_begin) + per > budget_s:
+                break
+    return g, times, iters, phases, scale
+
+
+def cpu_sample_text(workload, g, times, iters, scale):
+    per_iter = sum(times) / max(iters, 1)
+    if scale == 1.0:
+        return ("the full workload (%d factors): %d timed step(s) of %d LM iterations, %.3f s per iteration" % (g.n_factors, len(times), CPU_ITERS, per_iter))
+    return ("%d-frame slice of the workload's shape (%d factors; the full graph needs ~50 GB on the host): %d timed step(s) of %d LM iterations, "
+            "%.3f s per iteration on the slice, scaled by factor count x%.1f" % (CPU_SLICES[workload]["n_frames"], g.n_factors, len(times), CPU_ITERS, per_iter, scale))
 
 
 def run_reference(args, rank):
     """--impl reference: the reference's CPU path for this metric. GTSAM 4.2.0 is absent and cannot be
-    installed offline, so this times the restated oracle (oracle/, OpenMP over the host cores)."""
+    installed offline, so this times the restated oracle (oracle/, OpenMP over all host cores) on the same graph."""
     if rank != 0:
         return
     import oracle_lib
     oracle_lib.build()
     cores = set_host_threads(os.cpu_count() or 1)   # rank 0 alone runs: all host cores
     _, full = build_graph(WORKLOADS[args.workload])
-    g, times, iters = cpu_oracle_run(args.steps, args.warmup, args.workload)
-    per_iter_sample = sum(times) / max(iters, 1)
-    scale = full.n_factors / g.n_factors          # cost is linear in frames for this shape
-    value = 1.0 / (per_iter_sample * scale)
-    sample = ("%d-frame slice of the workload's shape (%d factors of %d), %d LM iterations per step, %.3f s per iteration on the slice; "
-              "value = slice rate scaled by factor count" % (CPU_SAMPLES.get(args.workload, CPU_SAMPLE)["n_frames"], g.n_factors, full.n_factors, CPU_SAMPLE_ITERS, per_iter_sample))
+    g, times, iters, phases, scale = cpu_oracle_run(args.steps, min(args.warmup, 1), args.workload, full, CPU_TIME_BUDGET_S)
+    per_iter = sum(times) / max(iters, 1)
+    value = 1.0 / (per_iter * scale)
     line = {
         "impl": "reference", "metric": "full-batch LM iterations/s", "value": value, "unit": "iter/s", "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / max(len(times), 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic", "config": {"workload": WORKLOAD_NAMES[args.workload], "formulation": "MotionInWorld (world-centric)"},
-        "cpu_baseline": {"value": value, "unit": "iter/s", "cores": cores, "kind": "port", "sample": sample},
+        "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / max(len(times), 1), "higher_is_better": True, "scaling": "strong" if args.gpus > 1 else "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": common_config(args.workload, full),
+        "cpu_baseline": {"value": value, "unit": "iter/s", "cores": cores, "kind": "port", "sample": cpu_sample_text(args.workload, g, times, iters, scale),
+                         "phase_s_per_iteration": {k: v / max(iters, 1) for k, v in phases.items()},
+                         "what": "restated CPU oracle (oracle/): not GTSAM, which is unavailable on this box"},
+        "steps_timed": len(times), "lm_iterations_per_step": CPU_ITERS,
         "e2e": {"value": value, "unit": "iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -228,7 +261,7 @@ def run_ours(args, rank, world, local_rank):
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
             dist.barrier()
             torch.cuda.synchronize()
-    sharded_mode = bool(args.sharded) and world > 1
+    sharded_mode = world > 1 and not args.replicas
     p = lm_params(local_rank)
     if sharded_mode:
         # ONE scene, partitioned by object and landmark over the ranks: strong scaling
@@ -277,6 +310,7 @@ def run_ours(args, rank, world, local_rank):
     clocks = sampler.stop()
     final_error = lm.error()
     tinfo = lm.timing()
+    residual = lm.solve_residual()   # |rhs - S x| / |rhs| of the reduced solves of the last optimize(), by the matrix-free operator
     # accuracy against the synthetic ground truth, outside the timed region
     accuracy = {"initial": d.metrics.evaluate(scene, g.pose_keys, g.pose_Rt), "final": d.metrics.evaluate(scene, g.pose_keys, lm.values()[0])}
 
@@ -353,23 +387,30 @@ def run_ours(args, rank, world, local_rank):
     dominant = max(kernels, key=lambda k: kernels[k]["ms"] * (n_lin if k.startswith("linearise") else n_sol))
     roofline = dict(kernels[dominant], kernel=dominant)
 
-    # CPU baseline beside the GPU number (N = 1 only), bounded sample
+    # CPU baseline beside the GPU number (N = 1 only): one step of the same workload on the host cores
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        set_host_threads(os.cpu_count() or 1)
-        sg, times, it = cpu_oracle_run(1, 0, args.workload)
+        cores = set_host_threads(os.cpu_count() or 1)
+        sg, times, it, phases, scale = cpu_oracle_run(1, 0, args.workload, g)
         per_iter = sum(times) / max(it, 1)
-        scale = g.n_factors / sg.n_factors
-        cpu_baseline = {"value": 1.0 / (per_iter * scale), "unit": "iter/s", "cores": os.cpu_count() or 1, "kind": "port",
-                        "sample": "%d-frame slice of the workload's shape (%d of %d factors), %d LM iterations, %.3f s per iteration on the slice, scaled by factor count"
-                                  % (CPU_SAMPLES.get(args.workload, CPU_SAMPLE)["n_frames"], sg.n_factors, g.n_factors, CPU_SAMPLE_ITERS, per_iter)}
+        cpu_baseline = {"value": 1.0 / (per_iter * scale), "unit": "iter/s", "cores": cores, "kind": "port", "sample": cpu_sample_text(args.workload, sg, times, it, scale),
+                        "phase_s_per_iteration": {k: v / max(it, 1) for k, v in phases.items()},
+                        "what": "restated CPU oracle (oracle/): not GTSAM, which is unavailable on this box"}
+    verify = None
+    if args.verify and world == 1:
+        from oracle_lib import OracleGraph
+        set_host_threads(os.cpu_count() or 1)
+        ora = OracleGraph.from_graph(g)
+        r = ora.optimize(max_iterations=LM_ITERS, relative_error_tol=0.0, absolute_error_tol=0.0)
+        verify = {"oracle_final_chi2": r["final_error"], "relative_difference": abs(final_error - r["final_error"]) / abs(r["final_error"]),
+                  "oracle_iterations": r["iterations"], "oracle_inner_iterations": r["inner_iterations"], "iterations": lm.iterations(), "inner_iterations": lm.getInnerIterations()}
 
     line = {
         "metric": "full-batch LM iterations/s", "value": value, "unit": "iter/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong" if sharded_mode else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[args.workload], "formulation": "MotionInWorld (world-centric; the fork has no hybrid formulation)",
-                   "lm_iterations_per_step": LM_ITERS, "factors": g.n_factors, "measurements": g.n_p2p, "poses": g.n_pose, "points": g.n_point,
-                   "reduced_dim": int(tinfo["reduced_dim"]), "half_bandwidth": int(tinfo["half_bandwidth"]),
+        "config": common_config(args.workload, g),
+        "lm_iterations_per_step": LM_ITERS,
+        "solver": {"reduced_dim": int(tinfo["reduced_dim"]), "half_bandwidth": int(tinfo["half_bandwidth"]),
                    "band_fronts": tinfo["band_fronts"], "band_split": tinfo["band_split"], "band_separator": tinfo["band_separator"],
                    "band_single_front_repeats": tinfo["band_single_front_repeats"],
                    "l2": "inputs larger than L2 (band %d MiB + graph and caches), no flush" % (int(tinfo["band_bytes"]) >> 20),
@@ -381,7 +422,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": launches,
         "roofline": roofline, "roofline_all": kernels, "cpu_baseline": cpu_baseline,
         "factor_linearisations_per_s": g.n_factors / (lin_ms * 1e-3),
-        "wall_ms_per_step": wall_ms / args.steps, "final_chi2": final_error, "accuracy": accuracy,
+        "wall_ms_per_step": wall_ms / args.steps, "final_chi2": final_error, "solve_residual": residual, "verify": verify, "accuracy": accuracy,
         "phase_ms_per_iteration": {k: phase[k] / max(iters if sharded_mode else iters / world, 1)
                                    for k in ("linearize_ms", "schur_assemble_ms", "band_cholesky_ms", "band_solve_ms", "evaluate_ms", "band_allreduce_ms")},
     }
@@ -477,7 +518,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + ["cfg4"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--sharded", action="store_true", help="N > 1: one scene partitioned over the GPUs (strong scaling) instead of N independent replicas")
+    ap.add_argument("--sharded", action="store_true", help="(default for N > 1) one scene partitioned over the GPUs by object and landmark: strong scaling")
+    ap.add_argument("--replicas", action="store_true", help="N > 1: N independent replicas of the workload (weak scaling, no data-path collective) instead of the sharded solve")
+    ap.add_argument("--verify", action="store_true", help="also run the CPU oracle with the same iteration budget on the same graph and print its chi^2 beside final_chi2")
     args = ap.parse_args()
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
