@@ -73,6 +73,15 @@ struct DeviceGraph {
   const int* seg_lo = nullptr;         // [n_seg] first incidence of the segment within the pose's concatenated list
   const int* pose_seg_ptr = nullptr;   // [n_pose + 1] segments of a pose (consecutive)
   const int* multi_pose = nullptr;     // [n_multi] poses with more than one segment
+  // Regular dynamic tracklets (every point of a chain has one PoseToPoint factor, cameras and motions of a chain follow one
+  // another in time: what the reference's formulation emits): the gather assembly of the reduced system (k_chain_theta,
+  // k_schur_chain_gather). step of a slot within its chain (-1: static landmark or padding), first block of the slot's
+  // rows in the Theta buffer, and per camera pose the ranges of its PoseToPoint list that belong to one object each.
+  const int* slot_step = nullptr;      // [n_slots]
+  const long long* theta_off = nullptr;// [n_slots] in 3 x 3 blocks
+  const int* cam_grp_ptr = nullptr;    // [n_pose + 1] object groups of a camera pose
+  const int* cam_grp_lo = nullptr;     // [groups] range [lo, hi) within pose_p2p_idx, chains deepest first
+  const int* cam_grp_hi = nullptr;
 };
 
 // Per-linearisation cache and normal-equation blocks.

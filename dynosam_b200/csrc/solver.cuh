@@ -391,6 +391,11 @@ class LmSolver {
   DevBuf<int> d_p2p_entry_of_input_, d_ter_slot_of_input_;
   DevBuf<int> d_seg_pose_, d_seg_lo_, d_pose_seg_ptr_, d_multi_pose_;   // segments of the pose-side gathers
   DevBuf<int> d_pose_nstatic_;
+  DevBuf<int> d_slot_step_, d_cam_grp_ptr_, d_cam_grp_lo_, d_cam_grp_hi_;
+  DevBuf<long long> d_theta_off_;
+  DevBuf<double> d_Theta_;                    // Theta rows of the gather assembly (72 bytes a block)
+  bool chains_regular_ = false, static_regular_ = false, use_gather_ = false;
+  long long theta_blocks_ = 0;
   int static_dmax_ = 0, static_both_sides_ = 0;
   DevBuf<double> d_seg_part_;                                           // [n_seg][27] partial sums of the poses with several segments
   // work

@@ -128,4 +128,31 @@ if __name__ == "__main__":
            "known_keys": {"X0": str(X(0)), "l0": str(l(0)), "m_frame2_tracklet3": str(m(2, 3)), "H_object1_frame2": str(H(1, 2))}}
     with open(os.path.join(HERE, "three_frame.json"), "w") as f:
         json.dump(out, f, indent=1)
+    # the same first graph as C arrays for tests/abi_smoke.c (a GTSAM-free C client of the C ABI)
+    g = out["graph"]
+
+    def arr(ctype, name, values):
+        flat = np.asarray(values).reshape(-1).tolist()
+        fmt = "%.17g" if ctype == "double" else "%d"
+        body = ", ".join((fmt % v) if ctype != "uint64_t" else ("%dULL" % int(v)) for v in flat)
+        return "static const %s %s[] = {%s};\n" % (ctype, name, body)
+
+    with open(os.path.join(HERE, "three_frame.h"), "w") as f:
+        f.write("/* generated by tests/golden/make_three_frame.py from reference dynosam/test/test_rgbd_backend.cc:272-495; do not edit */\n")
+        f.write("#include <stdint.h>\n")
+        f.write("enum { TF_N_POSE = %d, TF_N_POINT = %d, TF_N_P2P = %d, TF_N_TER = %d, TF_N_BTW = %d, TF_N_PRI = %d };\n"
+                % (len(g["pose_keys"]), len(g["point_keys"]), len(g["p2p"]), len(g["ternary"]), len(g["between"]), len(g["prior"])))
+        f.write("static const double TF_POINT_SIGMA = %.17g, TF_POSE_SIGMA = %.17g;\n" % (g["point_sigma"], g["pose_sigma"]))
+        f.write(arr("uint64_t", "tf_pose_keys", [int(k) for k in g["pose_keys"]]))
+        f.write(arr("double", "tf_pose_Rt", g["pose_Rt"]))
+        f.write(arr("uint64_t", "tf_point_keys", [int(k) for k in g["point_keys"]]))
+        f.write(arr("double", "tf_point_xyz", g["point_xyz"]))
+        f.write(arr("int32_t", "tf_p2p_pose", [r["pose"] for r in g["p2p"]]) + arr("int32_t", "tf_p2p_point", [r["point"] for r in g["p2p"]]))
+        f.write(arr("int32_t", "tf_p2p_order", [r["order"] for r in g["p2p"]]) + arr("double", "tf_p2p_z", [r["z"] for r in g["p2p"]]))
+        f.write(arr("int32_t", "tf_ter_prev", [r["prev"] for r in g["ternary"]]) + arr("int32_t", "tf_ter_cur", [r["cur"] for r in g["ternary"]]))
+        f.write(arr("int32_t", "tf_ter_motion", [r["motion"] for r in g["ternary"]]) + arr("int32_t", "tf_ter_order", [r["order"] for r in g["ternary"]]))
+        f.write(arr("int32_t", "tf_btw_a", [r["a"] for r in g["between"]]) + arr("int32_t", "tf_btw_b", [r["b"] for r in g["between"]]))
+        f.write(arr("int32_t", "tf_btw_order", [r["order"] for r in g["between"]]) + arr("double", "tf_btw_z", [r["z"] for r in g["between"]]))
+        f.write(arr("int32_t", "tf_pri_a", [r["a"] for r in g["prior"]]) + arr("int32_t", "tf_pri_order", [r["order"] for r in g["prior"]]))
+        f.write(arr("double", "tf_pri_z", [r["z"] for r in g["prior"]]))
     print("wrote three_frame.json:", {k: len(out["graph"][k]) for k in ("pose_keys", "point_keys", "p2p", "ternary", "between", "prior")})

@@ -301,3 +301,33 @@ def test_static_assembly_on_irregular_tracks(drop_gaps, shuffle):
     r = ora.optimize(max_iterations=4)
     np.testing.assert_allclose(lm.error_trace, r["error_trace"][:len(lm.error_trace)], rtol=CHI2_RTOL)
     assert lm.timing()["band_single_front_repeats"] == 0
+
+
+@pytest.mark.gpu
+def test_duplicate_static_observation_matches_oracle():
+    """Two PoseToPoint factors of one static landmark on the SAME pose (GTSAM accepts that): the mirrored half of the
+    diagonal Schur block must be there (k_schur_static with both_sides)."""
+    from types import SimpleNamespace
+    g = scenes.small_noisy().full_batch_graph()
+    static = np.flatnonzero(np.array([d.key_decode(int(k))[0] for k in g.point_keys])[g.p2p_point] == "l")
+    dup = static[::17]
+    c = SimpleNamespace(**{k: getattr(g, k) for k in ("pose_keys", "pose_Rt", "point_keys", "point_xyz", "n_pose", "n_point", "ter_prev", "ter_cur", "ter_motion", "ter_sigma",
+                                                      "ter_huber", "ter_order", "n_ternary", "btw_a", "btw_b", "btw_z", "btw_sigmas", "btw_order", "n_between", "pri_a", "pri_z",
+                                                      "pri_sigmas", "pri_order", "n_prior")})
+    cat = lambda a, extra: np.concatenate([a, extra])   # noqa: E731
+    c.p2p_pose, c.p2p_point = cat(g.p2p_pose, g.p2p_pose[dup]), cat(g.p2p_point, g.p2p_point[dup])
+    c.p2p_z = np.concatenate([g.p2p_z, g.p2p_z[dup] + 0.01])
+    c.p2p_sigma, c.p2p_huber = cat(g.p2p_sigma, g.p2p_sigma[dup]), cat(g.p2p_huber, g.p2p_huber[dup])
+    c.p2p_order = cat(g.p2p_order, np.arange(len(dup), dtype=np.int32) + g.n_factors)
+    c.n_p2p = len(c.p2p_pose)
+    c.n_factors = c.n_p2p + c.n_ternary + c.n_between + c.n_prior
+    c.pose_frames = g.pose_frames
+    gpu = d.GpuLevenbergMarquardt(None)
+    gpu.load_host_arrays(c)
+    ora = OracleGraph.from_graph(c)
+    assert gpu.error() == pytest.approx(ora.error(), rel=1e-12)
+    for lam in (1e-4, 1.0):
+        ok_g, dp_g, dpt_g, _ = gpu.solve_once(lam)
+        ok_c, dp_c, dpt_c = ora.solve_once(lam)
+        assert ok_g and ok_c
+        assert rel_err(dp_g, dp_c) <= 1e-7 and rel_err(dpt_g, dpt_c) <= 1e-7, (lam, rel_err(dp_g, dp_c), rel_err(dpt_g, dpt_c))

@@ -84,7 +84,6 @@ def test_config5_shaped_scene_matches_oracle():
     _compare(g, 3)
 
 
-@pytest.mark.xfail(reason="the chain part of the Schur assembly still adds into the band with floating-point atomics", strict=False)
 def test_repeated_solves_are_bit_identical():
     """The Schur assembly is a gather with one writer per block (no floating-point atomics): the same graph solved twice,
     in one handle and in two, gives the same bits."""
