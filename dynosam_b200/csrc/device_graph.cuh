@@ -82,6 +82,9 @@ struct DeviceGraph {
   const int* cam_grp_ptr = nullptr;    // [n_pose + 1] object groups of a camera pose
   const int* cam_grp_lo = nullptr;     // [groups] range [lo, hi) within pose_p2p_idx, chains deepest first
   const int* cam_grp_hi = nullptr;
+  // per incidence, in the order of pose_p2p_idx / pose_ter_idx: (PoseToPoint entry or -1, slot, step, first Theta block of the row)
+  const int4* grec_p2p = nullptr;
+  const int4* grec_ter = nullptr;
 };
 
 // Per-linearisation cache and normal-equation blocks.

@@ -467,17 +467,16 @@ __device__ __forceinline__ void warp_reduce36(double (&v)[36], int lane, int& e0
 // lists are sorted deepest first). ROW_CAM: the list holds PoseToPoint entries of a camera pose, else ternary slots of a
 // motion pose. PART_CAM: the partner is the camera of point t - d, else the motion of the link (t - d - 1, t - d).
 template <bool ROW_CAM, bool PART_CAM>
-__device__ __forceinline__ void gather_accumulate(double (&acc)[36], const DeviceGraph& g, const int* __restrict__ list, int n, int d, const double* __restrict__ Ru,
-                                                  const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw, const int* __restrict__ p2p_slot,
-                                                  const double* __restrict__ Theta, int lane) {
+__device__ __forceinline__ void gather_accumulate(double (&acc)[36], const DeviceGraph& g, const int4* __restrict__ list, int n, int d, const double* __restrict__ Ru,
+                                                  const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw, const double* __restrict__ Theta, int lane) {
   for (int i = lane; i < n; i += 32) {
-    int s;
-    double4 ca;
-    if (ROW_CAM) { const int e = list[i]; ca = p2p_qw[e]; s = p2p_slot[e]; }
-    else { s = list[i]; ca = ter_qw[s]; }
-    const int t = g.slot_step[s];
+    const int4 rec = list[i];   // (entry, slot, step, first Theta block of this row)
+    const int s = rec.y, t = rec.z;
     if (t < d + (PART_CAM ? 0 : 1)) break;   // sorted deepest first: nothing further reaches the partner
-    const double* th = Theta + 9 * ((size_t)g.theta_off[s] + (ROW_CAM ? 0 : (t + 1)) + d);
+    const double* th = Theta + 9 * ((size_t)rec.w + d);
+    const int sp = s - 32 * d;
+    const double4 ca = ROW_CAM ? p2p_qw[rec.x] : ter_qw[s];
+    const double4 cu = PART_CAM ? p2p_qw[g.row_base[sp >> 5] + (sp & 31)] : ter_qw[sp];
     double Th[9], Om[9];
     m3_load9(Th, th);
 #pragma unroll
@@ -488,8 +487,6 @@ __device__ __forceinline__ void gather_accumulate(double (&acc)[36], const Devic
 #pragma unroll
       for (int k = 0; k < 9; ++k) Om[k] -= th[9 + k];
     }
-    const int sp = s - 32 * d;
-    const double4 cu = PART_CAM ? p2p_qw[g.row_base[sp >> 5] + (sp & 31)] : ter_qw[sp];
     const double ww = ca.w * cu.w;
     const V3 va = v3(ca.x, ca.y, ca.z), vu = v3(cu.x, cu.y, cu.z);
     // A = [va]x Omega (column by column), B = Omega [vu]x (row by row), C = A [vu]x
@@ -534,9 +531,9 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
   // ---- motion row: the ternary factors this pose is the motion of ----
   const int n_mot = g.pose_ter_ptr[a + 1] - g.pose_ter_ptr[a];
   if (n_mot > 0) {
-    const int* list = g.pose_ter_idx + g.pose_ter_ptr[a];
-    const int s0 = list[0];
-    const int tmax = g.slot_step[s0];
+    const int4* list = g.grec_ter + g.pose_ter_ptr[a];
+    const int s0 = list[0].y;
+    const int tmax = list[0].z;
     if (tmax >= 1) {
       for (int it = wid; it < 2 * tmax; it += nw) {
         const bool part_cam = (it & 1) != 0;
@@ -545,8 +542,8 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
         const int u = part_cam ? g.p2p_pose[g.row_base[sp >> 5] + (sp & 31)] : g.ter_motion[sp];
         m3_load9(Ru, pose_lin + 12 * (size_t)u);
         clear();
-        if (part_cam) gather_accumulate<false, true>(acc, g, list, n_mot, d, Ru, p2p_qw, ter_qw, p2p_slot, Theta, lane);
-        else gather_accumulate<false, false>(acc, g, list, n_mot, d, Ru, p2p_qw, ter_qw, p2p_slot, Theta, lane);
+        if (part_cam) gather_accumulate<false, true>(acc, g, list, n_mot, d, Ru, p2p_qw, ter_qw, Theta, lane);
+        else gather_accumulate<false, false>(acc, g, list, n_mot, d, Ru, p2p_qw, ter_qw, Theta, lane);
         gather_commit(acc, bm, p, bs.pose_pos[u], lane);
       }
     }
@@ -555,7 +552,7 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
   const int g0 = g.cam_grp_ptr[a], g1 = g.cam_grp_ptr[a + 1];
   if (g1 > g0) {
     int dmax = 0;
-    for (int k = g0; k < g1; ++k) dmax = max(dmax, g.slot_step[p2p_slot[g.pose_p2p_idx[g.cam_grp_lo[k]]]]);
+    for (int k = g0; k < g1; ++k) dmax = max(dmax, g.grec_p2p[g.cam_grp_lo[k]].z);
     const int n_items = (dmax + 1) + (g1 - g0) * dmax;
     for (int it = wid; it < n_items; it += nw) {
       if (it <= dmax) {   // camera partner d points back: every object contributes to the same block
@@ -563,26 +560,26 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
         int u = -1;
         clear();
         for (int k = g0; k < g1; ++k) {
-          const int* list = g.pose_p2p_idx + g.cam_grp_lo[k];
-          const int s0 = p2p_slot[list[0]];
-          if (g.slot_step[s0] < d) continue;
+          const int4* list = g.grec_p2p + g.cam_grp_lo[k];
+          const int s0 = list[0].y;
+          if (list[0].z < d) continue;
           if (u < 0) {
             const int sp = s0 - 32 * d;
             u = g.p2p_pose[g.row_base[sp >> 5] + (sp & 31)];
             m3_load9(Ru, pose_lin + 12 * (size_t)u);
           }
-          gather_accumulate<true, true>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, Ru, p2p_qw, ter_qw, p2p_slot, Theta, lane);
+          gather_accumulate<true, true>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, Ru, p2p_qw, ter_qw, Theta, lane);
         }
         if (u >= 0) gather_commit(acc, bm, p, bs.pose_pos[u], lane);
       } else {            // motion partner of one object: the link (t - d - 1, t - d)
         const int k = g0 + (it - dmax - 1) / dmax, d = (it - dmax - 1) % dmax;
-        const int* list = g.pose_p2p_idx + g.cam_grp_lo[k];
-        const int s0 = p2p_slot[list[0]];
-        if (g.slot_step[s0] < d + 1) continue;
+        const int4* list = g.grec_p2p + g.cam_grp_lo[k];
+        const int s0 = list[0].y;
+        if (list[0].z < d + 1) continue;
         const int u = g.ter_motion[s0 - 32 * d];
         m3_load9(Ru, pose_lin + 12 * (size_t)u);
         clear();
-        gather_accumulate<true, false>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, Ru, p2p_qw, ter_qw, p2p_slot, Theta, lane);
+        gather_accumulate<true, false>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, Ru, p2p_qw, ter_qw, Theta, lane);
         gather_commit(acc, bm, p, bs.pose_pos[u], lane);
       }
     }

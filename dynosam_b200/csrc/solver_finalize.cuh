@@ -309,6 +309,23 @@ inline void LmSolver::finalize() {
       for (int i = pt_ptr[a]; i < pt_ptr[a + 1]; ++i) pt_idx[i] = (int)(pt_key[i] & 0xffffffffull);
     }
   }
+  // incidence records of the gather assembly, in list order: one 16-byte load instead of a chain of dependent index loads
+  std::vector<int4> grec_p2p, grec_ter;
+  if (regular && theta_blocks < 0x7fffffffLL) {
+    grec_p2p.resize(pp_idx.size()); grec_ter.resize(pt_idx.size());
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < (int64_t)pp_idx.size(); ++i) {
+      const int e = pp_idx[i], slot = p2p_slot[e], t = slot_step[slot];
+      grec_p2p[i] = make_int4(e, slot, t, t >= 0 ? (int)theta_off[slot] : 0);
+    }
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < (int64_t)pt_idx.size(); ++i) {
+      const int slot = pt_idx[i], t = slot_step[slot];
+      grec_ter[i] = make_int4(-1, slot, t, (int)theta_off[slot] + t + 1);
+    }
+  } else {
+    regular = false;
+  }
   lap(3);
   build_csr(2 * n_btw, [&](int i) { return (i & 1) ? h_btw_b_[i >> 1] : h_btw_a_[i >> 1]; }, [&](int i) { return i; }, pb_ptr, pb_idx);
   build_csr(n_pri, [&](int i) { return h_pri_a_[i]; }, [&](int i) { return i; }, pr_ptr, pr_idx);
@@ -343,6 +360,7 @@ inline void LmSolver::finalize() {
   d_pose_nstatic_.upload(pose_nstatic, stream_);
   d_slot_step_.upload(slot_step, stream_); d_theta_off_.upload(theta_off, stream_);
   d_cam_grp_ptr_.upload(cam_grp_ptr, stream_); d_cam_grp_lo_.upload(cam_grp_lo, stream_); d_cam_grp_hi_.upload(cam_grp_hi, stream_);
+  d_grec_p2p_.upload(grec_p2p, stream_); d_grec_ter_.upload(grec_ter, stream_);
   chains_regular_ = regular; theta_blocks_ = theta_blocks;
   d_seg_pose_.upload(seg_pose, stream_); d_seg_lo_.upload(seg_lo, stream_); d_pose_seg_ptr_.upload(pose_seg_ptr, stream_); d_multi_pose_.upload(multi_pose, stream_);
   // state
@@ -393,7 +411,7 @@ inline void LmSolver::finalize() {
   g_.pose_p2p_ptr = d_pose_p2p_ptr_.p; g_.pose_p2p_idx = d_pose_p2p_idx_.p; g_.pose_ter_ptr = d_pose_ter_ptr_.p; g_.pose_ter_idx = d_pose_ter_idx_.p;
   g_.pose_btw_ptr = d_pose_btw_ptr_.p; g_.pose_btw_idx = d_pose_btw_idx_.p; g_.pose_pri_ptr = d_pose_pri_ptr_.p; g_.pose_pri_idx = d_pose_pri_idx_.p;
   g_.pose_p2p_nstatic = d_pose_nstatic_.p;
-  g_.slot_step = d_slot_step_.p; g_.theta_off = d_theta_off_.p; g_.cam_grp_ptr = d_cam_grp_ptr_.p; g_.cam_grp_lo = d_cam_grp_lo_.p; g_.cam_grp_hi = d_cam_grp_hi_.p;
+  g_.slot_step = d_slot_step_.p; g_.theta_off = d_theta_off_.p; g_.cam_grp_ptr = d_cam_grp_ptr_.p; g_.cam_grp_lo = d_cam_grp_lo_.p; g_.cam_grp_hi = d_cam_grp_hi_.p; g_.grec_p2p = d_grec_p2p_.p; g_.grec_ter = d_grec_ter_.p;
   g_.n_seg = (int)seg_pose.size(); g_.n_multi = (int)multi_pose.size();
   g_.seg_pose = d_seg_pose_.p; g_.seg_lo = d_seg_lo_.p; g_.pose_seg_ptr = d_pose_seg_ptr_.p; g_.multi_pose = d_multi_pose_.p;
   d_seg_part_.alloc(27 * seg_pose.size());
