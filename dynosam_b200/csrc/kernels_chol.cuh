@@ -384,6 +384,12 @@ __device__ __forceinline__ void cp_async8(double* dst, const double* src, bool v
   const int sz = valid ? 8 : 0;   // src-size 0: zero fill
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
 }
+// 16 bytes (two adjacent columns): the band storage keeps element (r, c) with c even 16-byte aligned in every row (bw even)
+__device__ __forceinline__ void cp_async16(double* dst, const double* src, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  const int sz = valid ? 16 : 0;   // src-size 0: zero fill
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
@@ -427,11 +433,13 @@ __device__ __forceinline__ void chol_update_tile(const BandSystem& bs, int j0, i
     const double* rowp = S + (size_t)ir * ld + (bw - ir);
 #pragma unroll
     for (int bj = 0; bj < 4; ++bj)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int ic = c0 + wc + 8 * bj + 2 * fk + e;
-        acc[bi][bj][e] = (!idle && ir < i_end && ic <= ir) ? rowp[ic] : 0.0;
-      }
+    {
+      const int ic = c0 + wc + 8 * bj + 2 * fk;   // even: the pair (ic, ic + 1) is one aligned 16-byte word
+      double2 v = make_double2(0.0, 0.0);
+      if (!idle && ir < i_end && ic <= ir) v = *reinterpret_cast<const double2*>(rowp + ic);
+      acc[bi][bj][0] = v.x;
+      acc[bi][bj][1] = (ic + 1 <= ir) ? v.y : 0.0;
+    }
   }
   // Rows of the same 64-row block have very different envelopes (a camera pose reaches back over the life of its static
   // landmarks, an object motion only over its tracks), so a tile inside the block envelope is still about half zeros.
@@ -452,14 +460,14 @@ __device__ __forceinline__ void chol_update_tile(const BandSystem& bs, int j0, i
       for (int q = 0; q < 4; ++q) masks |= (((la >> (8 * q)) & 0xffu) ? 1u << q : 0u) << (8 * ch) | (((lb >> (8 * q)) & 0xffu) ? 16u << q : 0u) << (8 * ch);
     }
   }
-  const int kk = gtid & 15, rb = gtid >> 4;
+  const int kk = 2 * (gtid & 7), rb = gtid >> 3;   // a thread moves two adjacent columns of 4 (+4) rows per chunk
   auto stage = [&](int ch, double* buf) {
 #pragma unroll
-    for (int q = 0; q < 8; ++q) {
-      const int rr = rb + 8 * q, ir = r0 + rr, ic = c0 + rr;
+    for (int q = 0; q < 4; ++q) {
+      const int rr = rb + 16 * q, ir = r0 + rr, ic = c0 + rr;
       const bool va = ir < i_end, vb = ic < i_end;
-      cp_async8(buf + rr * LDT + kk, va ? S + (size_t)ir * ld + (j0 + KC * ch + kk - ir + bw) : S, va);
-      if (!diag) cp_async8(buf + 64 * LDT + rr * LDT + kk, vb ? S + (size_t)ic * ld + (j0 + KC * ch + kk - ic + bw) : S, vb);
+      cp_async16(buf + rr * LDT + kk, va ? S + (size_t)ir * ld + (j0 + KC * ch + kk - ir + bw) : S, va);
+      if (!diag) cp_async16(buf + 64 * LDT + rr * LDT + kk, vb ? S + (size_t)ic * ld + (j0 + KC * ch + kk - ic + bw) : S, vb);
     }
   };
   DETAIL_MARK(dm, 5, dt);   // address arithmetic + issue of the C loads
@@ -510,12 +518,11 @@ __device__ __forceinline__ void chol_update_tile(const BandSystem& bs, int j0, i
     if (ir >= i_end) continue;
     double* rowp = S + (size_t)ir * ld + (bw - ir);
 #pragma unroll
-    for (int bj = 0; bj < 4; ++bj)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int ic = c0 + wc + 8 * bj + 2 * fk + e;
-        if (ic <= ir) rowp[ic] = acc[bi][bj][e];
-      }
+    for (int bj = 0; bj < 4; ++bj) {
+      const int ic = c0 + wc + 8 * bj + 2 * fk;
+      if (ic + 1 <= ir) *reinterpret_cast<double2*>(rowp + ic) = make_double2(acc[bi][bj][0], acc[bi][bj][1]);
+      else if (ic <= ir) rowp[ic] = acc[bi][bj][0];
+    }
   }
   DETAIL_MARK(dm, 10, dt);
 }
