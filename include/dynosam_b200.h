@@ -7,8 +7,9 @@
  * at reference dynosam/src/backend/RGBDBackendModule.cc:220-221 (full batch)
  * and :374-376 (sliding window), together with graph.error(values) at
  * :216, :222, :363, :383 and problem.iterations()/getInnerIterations() at
- * :224-229.  include/dynosam_b200/gtsam_adapter.hpp shows the C++ shim a
- * maintainer would compile against GTSAM to call these entry points.
+ * :224-229.  include/dynosam_b200/gtsam_adapter.hpp is the C++ shim a maintainer
+ * compiles against GTSAM to call these entry points (its GTSAM-free layer is built
+ * and tested here: tests/adapter_smoke.cpp).
  *
  * Conventions: plain pointers and sizes, caller-owned HOST buffers borrowed for
  * the duration of a call, status-code returns (no exceptions cross the ABI), a
