@@ -379,60 +379,90 @@ __device__ __forceinline__ void m3_mul_neg_gt(double* C, const double* A, const 
 
 __global__ void __launch_bounds__(128) k_chain_theta(DeviceGraph g, const double* __restrict__ pose_lin, const double* __restrict__ Sig, const double* __restrict__ SigOff,
                                                      const double* __restrict__ G, double* __restrict__ Theta) {
+  // A warp is one 32-slot row of a slice: the same step t for all its chains (lanes past a chain's end idle). A block of a
+  // lane's row is 72 contiguous bytes; the warp passes the 32 blocks of a step through shared memory so that every store
+  // instruction writes runs of 72 bytes instead of 32 scattered 8-byte words.
+  __shared__ double stage[4][32 * 9];
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= g.n_slots) return;
-  const int t = g.slot_step[s];
-  if (t < 0) return;
-  double* out = Theta + 9 * (size_t)g.theta_off[s];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int t = s < g.n_slots ? g.slot_step[s] : -1;
+  const unsigned valid = __ballot_sync(kFull, t >= 0);
+  if (valid == 0u) return;
+  const int tw = __shfl_sync(kFull, t, __ffs(valid) - 1);
+  const bool on = t >= 0;
+  const long long off = on ? g.theta_off[s] : 0;
+  double* stg = stage[wid];
+  auto emit = [&](const double* Th, int row_off, int d) {
+#pragma unroll
+    for (int i = 0; i < 9; ++i) stg[lane * 9 + i] = Th[i];
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const int idx = k * 32 + lane, b = idx / 9, e = idx - 9 * b;
+      const long long ob = __shfl_sync(kFull, off, b);
+      if ((valid >> b) & 1u) Theta[9 * (size_t)(ob + row_off + d) + e] = stg[idx];
+    }
+    __syncwarp();
+  };
   double Th[9], Nx[9], Gm[9];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) { Th[i] = 0.0; Gm[i] = 0.0; }
   {  // camera row: R_X^T Sigma_{t, t-d}
-    const int a = g.p2p_pose[g.row_base[s >> 5] + (s & 31)];
-    double R[9];
-    m3_load9(R, pose_lin + 12 * (size_t)a);
-    const M3 S = s3_full(s3_load(Sig + 6 * (size_t)s));
+    if (on) {
+      const int a = g.p2p_pose[g.row_base[s >> 5] + (s & 31)];
+      double R[9];
+      m3_load9(R, pose_lin + 12 * (size_t)a);
+      const M3 S = s3_full(s3_load(Sig + 6 * (size_t)s));
 #pragma unroll
-    for (int i = 0; i < 3; ++i)
+      for (int i = 0; i < 3; ++i)
 #pragma unroll
-      for (int j = 0; j < 3; ++j) Th[3 * i + j] = R[i] * S.a[j] + R[3 + i] * S.a[3 + j] + R[6 + i] * S.a[6 + j];
+        for (int j = 0; j < 3; ++j) Th[3 * i + j] = R[i] * S.a[j] + R[3 + i] * S.a[3 + j] + R[6 + i] * S.a[6 + j];
+    }
     for (int d = 0;; ++d) {
-#pragma unroll
-      for (int i = 0; i < 9; ++i) out[9 * (size_t)d + i] = Th[i];
-      if (d == t) break;
-      m3_load9(Gm, G + 9 * (size_t)(s - 32 * d));
+      emit(Th, 0, d);
+      if (d == tw) break;
+      if (on) m3_load9(Gm, G + 9 * (size_t)(s - 32 * d));
       m3_mul_neg_gt(Nx, Th, Gm);
 #pragma unroll
       for (int i = 0; i < 9; ++i) Th[i] = Nx[i];
     }
   }
-  if (t >= 1) {  // motion row of the link (t-1, t): -Sigma_{t-1, t-d} + R_H^T Sigma_{t, t-d}
-    out += 9 * (size_t)(t + 1);
-    const int h = g.ter_motion[s];
-    double R[9], So[9];
-    m3_load9(R, pose_lin + 12 * (size_t)h);
-    m3_load9(So, SigOff + 9 * (size_t)s);   // Sigma_{t-1, t}
-    const M3 St = s3_full(s3_load(Sig + 6 * (size_t)s));
-    const M3 Sp = s3_full(s3_load(Sig + 6 * (size_t)(s - 32)));
+  if (tw >= 1) {  // motion row of the link (t-1, t): -Sigma_{t-1, t-d} + R_H^T Sigma_{t, t-d}
 #pragma unroll
-    for (int i = 0; i < 3; ++i)
+    for (int i = 0; i < 9; ++i) { Th[i] = 0.0; Nx[i] = 0.0; }
+    if (on) {
+      const int h = g.ter_motion[s];
+      double R[9], So[9];
+      m3_load9(R, pose_lin + 12 * (size_t)h);
+      m3_load9(So, SigOff + 9 * (size_t)s);   // Sigma_{t-1, t}
+      const M3 St = s3_full(s3_load(Sig + 6 * (size_t)s));
+      const M3 Sp = s3_full(s3_load(Sig + 6 * (size_t)(s - 32)));
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        Th[3 * i + j] = -So[3 * i + j] + (R[i] * St.a[j] + R[3 + i] * St.a[3 + j] + R[6 + i] * St.a[6 + j]);                // d = 0
-        Nx[3 * i + j] = -Sp.a[3 * i + j] + (R[i] * So[3 * j] + R[3 + i] * So[3 * j + 1] + R[6 + i] * So[3 * j + 2]);        // d = 1: R^T Sigma_{t, t-1} = R^T SigOff^T
-      }
+      for (int i = 0; i < 3; ++i)
 #pragma unroll
-    for (int i = 0; i < 9; ++i) { out[i] = Th[i]; out[9 + i] = Nx[i]; Th[i] = Nx[i]; }
-    for (int d = 2; d <= t; ++d) {
-      m3_load9(Gm, G + 9 * (size_t)(s - 32 * (d - 1)));
+        for (int j = 0; j < 3; ++j) {
+          Th[3 * i + j] = -So[3 * i + j] + (R[i] * St.a[j] + R[3 + i] * St.a[3 + j] + R[6 + i] * St.a[6 + j]);                // d = 0
+          Nx[3 * i + j] = -Sp.a[3 * i + j] + (R[i] * So[3 * j] + R[3 + i] * So[3 * j + 1] + R[6 + i] * So[3 * j + 2]);        // d = 1: R^T Sigma_{t, t-1} = R^T SigOff^T
+        }
+    }
+    emit(Th, tw + 1, 0);
+    emit(Nx, tw + 1, 1);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) Th[i] = Nx[i];
+    for (int d = 2; d <= tw; ++d) {
+      if (on) m3_load9(Gm, G + 9 * (size_t)(s - 32 * (d - 1)));
       m3_mul_neg_gt(Nx, Th, Gm);
 #pragma unroll
-      for (int i = 0; i < 9; ++i) { Th[i] = Nx[i]; out[9 * (size_t)d + i] = Nx[i]; }
+      for (int i = 0; i < 9; ++i) Th[i] = Nx[i];
+      emit(Th, tw + 1, d);
     }
   }
 }
 
-// Sum of v[0..35] over the lanes of a warp by recursive halving: after five exchange steps every lane holds two of the
-// 36 sums (a few lanes hold padding). Returns the element indices of v[0], v[1] in e0, e1 (-1: padding).
-__device__ __forceinline__ void warp_reduce36(double (&v)[36], int lane, int& e0, int& e1) {
+// Sum of v[0..35] over the 8 lanes of a sub-warp group (lanes that differ in their low three bits) by recursive halving:
+// after three exchange steps every lane holds five of the 36 sums (v[0..4]; one slot of the odd lanes is padding).
+// All 32 lanes execute it. first = index of v[0] among the 36, count = how many of v[0..4] are real.
+__device__ __forceinline__ void group8_reduce36(double (&v)[36], int lane, int& first, int& count) {
   auto step = [&](int n, int s) {   // n even: keep n / 2 values, the lane with bit s set keeps the upper half
     const bool up = (lane & s) != 0;
     const int h = n >> 1;
@@ -445,45 +475,37 @@ __device__ __forceinline__ void warp_reduce36(double (&v)[36], int lane, int& e0
       }
     }
   };
-  step(36, 16);            // 18 left
-  step(18, 8);             // 9 left
-  v[9] = 0.0; step(10, 4); // 5 left
-  v[5] = 0.0; step(6, 2);  // 3 left
-  v[3] = 0.0; step(4, 1);  // 2 left
-  const int b4 = (lane >> 4) & 1, b3 = (lane >> 3) & 1, b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1, b0 = lane & 1;
-  auto elem = [&](int k) {
-    const int i5 = 2 * b0 + k;          // within the 3 (+1 padding)
-    if (i5 >= 3) return -1;
-    const int i4 = 3 * b1 + i5;         // within the 5 (+1 padding)
-    if (i4 >= 5) return -1;
-    const int i3 = 5 * b2 + i4;         // within the 9 (+1 padding)
-    if (i3 >= 9) return -1;
-    return 18 * b4 + 9 * b3 + i3;
-  };
-  e0 = elem(0); e1 = elem(1);
+  step(36, 4);             // 18 left
+  step(18, 2);             // 9 left
+  v[9] = 0.0; step(10, 1); // 5 left
+  const int b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1, b0 = lane & 1;
+  first = 18 * b2 + 9 * b1 + 5 * b0;
+  count = b0 ? 4 : 5;
 }
 
-// acc += w_a w_u F(q_a)^T Omega F(q_u) over the chains [lo, lo + n) of one list that reach back d points (a prefix: the
-// lists are sorted deepest first). ROW_CAM: the list holds PoseToPoint entries of a camera pose, else ternary slots of a
-// motion pose. PART_CAM: the partner is the camera of point t - d, else the motion of the link (t - d - 1, t - d).
-template <bool ROW_CAM, bool PART_CAM>
-__device__ __forceinline__ void gather_accumulate(double (&acc)[36], const DeviceGraph& g, const int4* __restrict__ list, int n, int d, const double* __restrict__ Ru,
-                                                  const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw, const double* __restrict__ Theta, int lane) {
-  for (int i = lane; i < n; i += 32) {
+// acc += w_a w_u F(q_a)^T Omega F(q_u) over the chains [0, n) of one list that reach back d points (a prefix: the lists are
+// sorted deepest first), dealt to the 8 lanes of a group. ROW_CAM: the list holds PoseToPoint incidences of a camera pose,
+// else ternary incidences of a motion pose. part_cam: the partner is the camera of point t - d, else the motion of the
+// link (t - d - 1, t - d) (uniform over the warp: the items of a batch are of one kind).
+template <bool ROW_CAM>
+__device__ __forceinline__ void gather_accumulate(double (&acc)[36], const DeviceGraph& g, const int4* __restrict__ list, int n, int d, bool part_cam,
+                                                  const double* __restrict__ Ru, const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
+                                                  const double* __restrict__ Theta, int sl) {
+  for (int i = sl; i < n; i += 8) {
     const int4 rec = list[i];   // (entry, slot, step, first Theta block of this row)
     const int s = rec.y, t = rec.z;
-    if (t < d + (PART_CAM ? 0 : 1)) break;   // sorted deepest first: nothing further reaches the partner
+    if (t < d + (part_cam ? 0 : 1)) break;   // sorted deepest first: nothing further reaches the partner
     const double* th = Theta + 9 * ((size_t)rec.w + d);
     const int sp = s - 32 * d;
     const double4 ca = ROW_CAM ? p2p_qw[rec.x] : ter_qw[s];
-    const double4 cu = PART_CAM ? p2p_qw[g.row_base[sp >> 5] + (sp & 31)] : ter_qw[sp];
+    const double4 cu = part_cam ? p2p_qw[g.row_base[sp >> 5] + (sp & 31)] : ter_qw[sp];
     double Th[9], Om[9];
     m3_load9(Th, th);
 #pragma unroll
     for (int r = 0; r < 3; ++r)
 #pragma unroll
       for (int c = 0; c < 3; ++c) Om[3 * r + c] = Th[3 * r] * Ru[c] + Th[3 * r + 1] * Ru[3 + c] + Th[3 * r + 2] * Ru[6 + c];
-    if (!PART_CAM) {
+    if (!part_cam) {
 #pragma unroll
       for (int k = 0; k < 9; ++k) Om[k] -= th[9 + k];
     }
@@ -508,21 +530,31 @@ __device__ __forceinline__ void gather_accumulate(double (&acc)[36], const Devic
   }
 }
 
-// block (p, pu) of the band -= the warp's sum of acc; the warp is the only writer of the block in this kernel
+// block (p, pu) of the band -= the group's sum of acc (pu < 0: the group had no item); the group is the only writer of the
+// block in this kernel. All 32 lanes call.
 __device__ __forceinline__ void gather_commit(double (&acc)[36], const BandMap& bm, int p, int pu, int lane) {
-  int e0, e1;
-  warp_reduce36(acc, lane, e0, e1);
-  if (e0 >= 0) { const int r = e0 / 6, c = e0 - 6 * r; if (pu < p || c <= r) *band_at(bm, 6 * p + r, 6 * pu + c) -= acc[0]; }
-  if (e1 >= 0) { const int r = e1 / 6, c = e1 - 6 * r; if (pu < p || c <= r) *band_at(bm, 6 * p + r, 6 * pu + c) -= acc[1]; }
+  int first, count;
+  group8_reduce36(acc, lane, first, count);
+  if (pu < 0) return;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+    if (k < count) {
+      const int e = first + k, r = e / 6, c = e - 6 * r;
+      if (pu < p || c <= r) *band_at(bm, 6 * p + r, 6 * pu + c) -= acc[k];
+    }
+  }
 }
 
+// One CTA per pose row. A warp takes a batch of four target blocks of one kind (consecutive depths) at a time, eight lanes
+// each: the lanes of a group share the chains of their block among them and keep 6 x 6 sums of their own.
 constexpr int kGatherThreads = 256;
 __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(DeviceGraph g, BandSystem bs, BandMap bm, const double* __restrict__ pose_lin,
-                                                                       const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
-                                                                       const int* __restrict__ p2p_slot, const double* __restrict__ Theta) {
+                                                                          const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
+                                                                          const int* __restrict__ p2p_slot, const double* __restrict__ Theta) {
   const int p = blockIdx.x;
   const int a = bs.pos_pose[p];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int sub = lane >> 3, sl = lane & 7;
   double acc[36], Ru[9];
   auto clear = [&]() {
 #pragma unroll
@@ -532,19 +564,23 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
   const int n_mot = g.pose_ter_ptr[a + 1] - g.pose_ter_ptr[a];
   if (n_mot > 0) {
     const int4* list = g.grec_ter + g.pose_ter_ptr[a];
-    const int s0 = list[0].y;
-    const int tmax = list[0].z;
+    const int s0 = list[0].y, tmax = list[0].z;
     if (tmax >= 1) {
-      for (int it = wid; it < 2 * tmax; it += nw) {
-        const bool part_cam = (it & 1) != 0;
-        const int d = part_cam ? 1 + (it >> 1) : (it >> 1);   // camera partners 1..tmax (the camera of the link's own point comes later in time), motion partners 0..tmax-1
-        const int sp = s0 - 32 * d;
-        const int u = part_cam ? g.p2p_pose[g.row_base[sp >> 5] + (sp & 31)] : g.ter_motion[sp];
-        m3_load9(Ru, pose_lin + 12 * (size_t)u);
+      const int nb = (tmax + 3) >> 2;   // batches per kind: camera partners d = 1..tmax, motion partners d = 0..tmax-1
+      for (int b = wid; b < 2 * nb; b += nw) {
+        const bool part_cam = b < nb;
+        const int k = 4 * (part_cam ? b : b - nb) + sub;      // 0..tmax-1 when valid
+        const bool valid = k < tmax;
+        const int d = part_cam ? k + 1 : k;
+        int u = -1;
         clear();
-        if (part_cam) gather_accumulate<false, true>(acc, g, list, n_mot, d, Ru, p2p_qw, ter_qw, Theta, lane);
-        else gather_accumulate<false, false>(acc, g, list, n_mot, d, Ru, p2p_qw, ter_qw, Theta, lane);
-        gather_commit(acc, bm, p, bs.pose_pos[u], lane);
+        if (valid) {
+          const int sp = s0 - 32 * d;
+          u = part_cam ? g.p2p_pose[g.row_base[sp >> 5] + (sp & 31)] : g.ter_motion[sp];
+          m3_load9(Ru, pose_lin + 12 * (size_t)u);
+          gather_accumulate<false>(acc, g, list, n_mot, d, part_cam, Ru, p2p_qw, ter_qw, Theta, sl);
+        }
+        gather_commit(acc, bm, p, valid ? bs.pose_pos[u] : -1, lane);
       }
     }
   }
@@ -553,35 +589,36 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
   if (g1 > g0) {
     int dmax = 0;
     for (int k = g0; k < g1; ++k) dmax = max(dmax, g.grec_p2p[g.cam_grp_lo[k]].z);
-    const int n_items = (dmax + 1) + (g1 - g0) * dmax;
-    for (int it = wid; it < n_items; it += nw) {
-      if (it <= dmax) {   // camera partner d points back: every object contributes to the same block
-        const int d = it;
-        int u = -1;
-        clear();
-        for (int k = g0; k < g1; ++k) {
-          const int4* list = g.grec_p2p + g.cam_grp_lo[k];
-          const int s0 = list[0].y;
-          if (list[0].z < d) continue;
-          if (u < 0) {
-            const int sp = s0 - 32 * d;
-            u = g.p2p_pose[g.row_base[sp >> 5] + (sp & 31)];
-            m3_load9(Ru, pose_lin + 12 * (size_t)u);
+    const int nb_xx = (dmax + 4) >> 2;        // camera partners d = 0..dmax: every object contributes to the same block
+    const int nb_xh = (dmax + 3) >> 2;        // motion partners of one object d = 0..tmax_k-1
+    const int n_batches = nb_xx + (g1 - g0) * nb_xh;
+    for (int b = wid; b < n_batches; b += nw) {
+      int u = -1;
+      clear();
+      if (b < nb_xx) {
+        const int d = 4 * b + sub;
+        if (d <= dmax) {
+          for (int k = g0; k < g1; ++k) {
+            const int4* list = g.grec_p2p + g.cam_grp_lo[k];
+            if (list[0].z < d) continue;
+            if (u < 0) {
+              const int sp = list[0].y - 32 * d;
+              u = g.p2p_pose[g.row_base[sp >> 5] + (sp & 31)];
+              m3_load9(Ru, pose_lin + 12 * (size_t)u);
+            }
+            gather_accumulate<true>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, true, Ru, p2p_qw, ter_qw, Theta, sl);
           }
-          gather_accumulate<true, true>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, Ru, p2p_qw, ter_qw, Theta, lane);
         }
-        if (u >= 0) gather_commit(acc, bm, p, bs.pose_pos[u], lane);
-      } else {            // motion partner of one object: the link (t - d - 1, t - d)
-        const int k = g0 + (it - dmax - 1) / dmax, d = (it - dmax - 1) % dmax;
+      } else {
+        const int k = g0 + (b - nb_xx) / nb_xh, d = 4 * ((b - nb_xx) % nb_xh) + sub;
         const int4* list = g.grec_p2p + g.cam_grp_lo[k];
-        const int s0 = list[0].y;
-        if (list[0].z < d + 1) continue;
-        const int u = g.ter_motion[s0 - 32 * d];
-        m3_load9(Ru, pose_lin + 12 * (size_t)u);
-        clear();
-        gather_accumulate<true, false>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, Ru, p2p_qw, ter_qw, Theta, lane);
-        gather_commit(acc, bm, p, bs.pose_pos[u], lane);
+        if (list[0].z >= d + 1) {
+          u = g.ter_motion[list[0].y - 32 * d];
+          m3_load9(Ru, pose_lin + 12 * (size_t)u);
+          gather_accumulate<true>(acc, g, list, g.cam_grp_hi[k] - g.cam_grp_lo[k], d, false, Ru, p2p_qw, ter_qw, Theta, sl);
+        }
       }
+      gather_commit(acc, bm, p, u >= 0 ? bs.pose_pos[u] : -1, lane);
     }
   }
 }
