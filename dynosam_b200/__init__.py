@@ -12,5 +12,6 @@ from .api import (  # noqa: F401
 )
 from . import graphfile  # noqa: E402,F401  (DynoSAM text graph file reader / writer)
 from . import metrics  # noqa: E402,F401  (ATE / RPE / object-motion error against scene ground truth)
+from . import postsolve  # noqa: E402,F401  (object pose propagation from the optimised motions, the reference logger CSV layout)
 from . import sharded  # noqa: E402,F401  (sharded solve over the GPUs of one box: partition, rank shares, NCCL exchange inside the library)
 from . import llworld  # noqa: E402,F401  (LLWorld formulation factors, batched evaluation on the device)
