@@ -103,10 +103,27 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+FORMULATION = "world"   # --formulation: "world" = MotionInWorld (what the fork emits); "hybrid" = the builder-defined object-centric one
+FORMULATION_NAMES = {
+    "world": "MotionInWorld (world-centric; the fork has no hybrid formulation)",
+    "hybrid": "hybrid / object-centric (builder-defined, parity self-pinned: one point per tracklet, emitted through T_k = H_k^-1 X_k as PoseToPoint factors, no motion smoothing)",
+}
+
+
 def build_graph(cfg):
     import dynosam_b200 as d
     scene = d.Scene.synthetic(**cfg)
-    return scene, scene.full_batch_graph()
+    return scene, (scene.hybrid_graph() if FORMULATION == "hybrid" else scene.full_batch_graph())
+
+
+def accuracy_of(scene, g, pose_Rt):
+    """ATE / RPE / object-motion error against the generator's ground truth; a hybrid solution is first turned into camera
+    poses and per-frame world motions (postsolve.hybrid_as_world_motion_values) so both formulations are measured alike."""
+    import dynosam_b200 as d
+    if FORMULATION == "hybrid":
+        keys, Rt = d.postsolve.hybrid_as_world_motion_values(g.pose_keys, pose_Rt)
+        return d.metrics.evaluate(scene, keys, Rt)
+    return d.metrics.evaluate(scene, g.pose_keys, pose_Rt)
 
 
 def lm_params(device=0):
@@ -121,7 +138,7 @@ def lm_params(device=0):
 
 def common_config(workload, g):
     """The part of `config` both arms print: same workload, same graph."""
-    return {"workload": WORKLOAD_NAMES[workload], "formulation": "MotionInWorld (world-centric; the fork has no hybrid formulation)",
+    return {"workload": WORKLOAD_NAMES[workload], "formulation": FORMULATION_NAMES[FORMULATION],
             "factors": g.n_factors, "measurements": g.n_p2p, "poses": g.n_pose, "points": g.n_point}
 
 
@@ -312,7 +329,7 @@ def run_ours(args, rank, world, local_rank):
     tinfo = lm.timing()
     residual = lm.solve_residual()   # |rhs - S x| / |rhs| of the reduced solves of the last optimize(), by the matrix-free operator
     # accuracy against the synthetic ground truth, outside the timed region
-    accuracy = {"initial": d.metrics.evaluate(scene, g.pose_keys, g.pose_Rt), "final": d.metrics.evaluate(scene, g.pose_keys, lm.values()[0])}
+    accuracy = {"initial": accuracy_of(scene, g, g.pose_Rt), "final": accuracy_of(scene, g, lm.values()[0])}
 
     # ---- end-to-end arm: host buffers through the C ABI ----
     if sharded_mode:
@@ -367,7 +384,7 @@ def run_ours(args, rank, world, local_rank):
         "linearise (k_point_factors + k_pose_factors + k_build_poses)": {
             "bound": "hbm", "achieved": lin_bytes(gs) / (lin_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "ms": lin_ms, "peak_source": hbm_src,
             "algorithmic_bytes": lin_bytes(gs), "traffic": None},
-        "schur assembly (k_schur_assemble)": {
+        "schur assembly (k_schur_init + k_schur_static + k_chain_theta + k_schur_chain_gather)": {
             "bound": "hbm", "achieved": schur_bytes(gs, tinfo["envelope_blocks"]) / (max(sch_ms, 1e-9) * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "ms": sch_ms,
             "peak_source": hbm_src, "algorithmic_bytes": schur_bytes(gs, tinfo["envelope_blocks"]), "traffic": None},
         "band cholesky (k_band_cholesky)": {
@@ -569,7 +586,12 @@ def main():
     ap.add_argument("--sharded", action="store_true", help="(default for N > 1) one scene partitioned over the GPUs by object and landmark: strong scaling")
     ap.add_argument("--replicas", action="store_true", help="N > 1: N independent replicas of the workload (weak scaling, no data-path collective) instead of the sharded solve")
     ap.add_argument("--verify", action="store_true", help="also run the CPU oracle with the same iteration budget on the same graph and print its chi^2 beside final_chi2")
+    ap.add_argument("--formulation", default="world", choices=["world", "hybrid"], help="world: MotionInWorld as the fork emits it; hybrid: the builder-defined object-centric formulation (full-batch workloads)")
     args = ap.parse_args()
+    global FORMULATION
+    FORMULATION = args.formulation
+    if FORMULATION == "hybrid" and args.workload == "cfg4":
+        raise SystemExit("bench.py: --formulation hybrid is defined for the full-batch workloads")
     rank, world, local_rank = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
         if args.workload == "cfg4":

@@ -9,6 +9,7 @@
 
 #include "host/partition.hpp"
 #include "host/scene.hpp"
+#include "host/formulation_hybrid.hpp"
 #include "solver.cuh"
 #include "kernels_llworld.cuh"
 

@@ -461,16 +461,20 @@ inline void LmSolver::setup_band(const std::vector<int>& chain_of_point) {
   // one row of lanes earlier (same slot).
   {
     // (>=: two factors of one landmark on the same pose also need both sides, for the mirrored half of the diagonal block.)
-    // Regular static tracks: consecutive observations of a landmark come from the cameras of consecutive frames; then a pose's
-    // partner o observations back is the same pose for all its landmarks (k_schur_static without atomics).
+    // Regular tracks: the observation before a pose's observation of a landmark comes from the SAME pose for every landmark
+    // of that pose (cameras of consecutive frames in the world-centric graphs; the object's previous virtual camera, or the
+    // keyframe camera, in the hybrid ones). By induction a pose's partner o observations back is then one pose for all its
+    // landmarks: k_schur_static has one writer per block and needs no atomics.
     int both = 0, irregular = 0;
+    std::vector<int> pred(np, -1);
 #pragma omp parallel for schedule(static) reduction(| : both, irregular)
     for (int64_t f = 0; f < n_p2p; ++f) {
       const int e = p2p_entry_of_input_[f];
       if (e >= 32 && hs_p2p_slot_[e - 32] == hs_p2p_slot_[e]) {
-        if (pose_pos[hs_p2p_pose_[e - 32]] >= pose_pos[hs_p2p_pose_[e]]) both |= 1;
-        const Key k1 = pose_keys_[hs_p2p_pose_[e - 32]], k2 = pose_keys_[hs_p2p_pose_[e]];
-        if (key_chr(k1) != kPoseSymbolChar || key_chr(k2) != kPoseSymbolChar || key_index(k2) != key_index(k1) + 1) irregular |= 1;
+        const int a0 = hs_p2p_pose_[e - 32], a1 = hs_p2p_pose_[e];
+        if (pose_pos[a0] >= pose_pos[a1]) both |= 1;
+        int expect = -1;
+        if (!__atomic_compare_exchange_n(&pred[a1], &expect, a0, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED) && expect != a0) irregular |= 1;
       }
     }
     static_both_sides_ = both;

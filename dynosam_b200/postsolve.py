@@ -173,3 +173,42 @@ def write_logs(directory, module_name, graph, pose_Rt, point_xyz, gt_camera=None
         w.writerow([frame if c == "m" else 0, int(o) if o >= 0 else 0, tracklet] + list(xyz))   # background label 0 for static points
     f.close()
     return paths
+
+
+def hybrid_motions(pose_keys, pose_Rt):
+    """Hybrid (object-centric) graphs carry T_j^k = H_{e->k}^-1 X_k as 'L'(object, frame) pose variables
+    (csrc/host/formulation_hybrid.hpp). -> (keyframe_motions {(object, frame): H_{e->k} = X_k T_k^-1},
+    frame_motions {(object, frame): H_{k-1->k} = H_{e->k} H_{e->k-1}^-1}); the keyframe itself has H = identity."""
+    cams, virt = {}, {}
+    for k, Rt in zip(pose_keys, pose_Rt):
+        c, obj, frame, _ = key_decode(int(k))
+        if c == "X":
+            cams[frame] = _T(Rt)
+        elif c == "L":
+            virt[(obj, frame)] = _T(Rt)
+    key_H = {}
+    for (obj, frame), T in virt.items():
+        key_H[(obj, frame)] = cams[frame] @ np.linalg.inv(T)
+    for obj in {o for o, _ in virt}:
+        first = min(f for o, f in virt if o == obj)
+        key_H[(obj, first - 1)] = np.eye(4)   # the keyframe: observed through the camera pose itself
+    frame_H = {}
+    for (obj, frame), H in key_H.items():
+        if (obj, frame - 1) in key_H:
+            frame_H[(obj, frame)] = H @ np.linalg.inv(key_H[(obj, frame - 1)])
+    return key_H, frame_H
+
+
+def hybrid_as_world_motion_values(pose_keys, pose_Rt):
+    """The camera poses and the per-frame world motions of a hybrid solution under the world-centric keys ('X', 'H'), so that
+    metrics.evaluate() measures both formulations against the same ground truth. -> (keys uint64[], Rt (n, 12))."""
+    from .api import ObjectMotionSymbol
+    keys, rows = [], []
+    for k, Rt in zip(pose_keys, pose_Rt):
+        if key_decode(int(k))[0] == "X":
+            keys.append(int(k)); rows.append(np.asarray(Rt, float))
+    _, frame_H = hybrid_motions(pose_keys, pose_Rt)
+    for (obj, frame), H in sorted(frame_H.items()):
+        keys.append(ObjectMotionSymbol(obj, frame))
+        rows.append(np.concatenate([H[:3, :3].reshape(-1), H[:3, 3]]))
+    return np.array(keys, dtype=np.uint64), np.array(rows).reshape(-1, 12)
