@@ -262,6 +262,45 @@ def replica_config(workload, rank):
     return cfg
 
 
+def measure_hybrid(args, local_rank):
+    """The same workload in the builder-defined hybrid (object-centric) formulation, beside the headline (world-centric) line:
+    device-resident LM iterations/s, end to end from host buffers, phase times, operator residual; N = 1 only."""
+    import torch
+    import dynosam_b200 as d
+    global FORMULATION
+    saved, FORMULATION = FORMULATION, "hybrid"
+    try:
+        scene, g = build_graph(WORKLOADS[args.workload])
+        lm = d.GpuLevenbergMarquardt(g, lm_params(local_rank))
+        for _ in range(args.warmup):
+            lm.reset_values(); lm.optimize()
+        dev_ms, iters, phase = 0.0, 0, {}
+        for _ in range(args.steps):
+            lm.reset_values(); lm.optimize()
+            t = lm.timing()
+            dev_ms += t["optimize_ms"]; iters += lm.iterations()
+            for k in ("linearize_ms", "schur_assemble_ms", "band_cholesky_ms", "band_solve_ms", "evaluate_ms", "n_linearize", "n_solves"):
+                phase[k] = phase.get(k, 0.0) + t.get(k, 0.0)
+        chi2, residual = lm.error(), lm.solve_residual()
+        acc = accuracy_of(scene, g, lm.values()[0])
+        e2e_lm = d.GpuLevenbergMarquardt(None, lm_params(local_rank))
+        e2e_s, e2e_iters = 0.0, 0
+        for s in range(2 + args.steps):
+            torch.cuda.synchronize(); t1 = time.perf_counter()
+            e2e_lm.load_host_arrays(g); e2e_lm.optimize()
+            torch.cuda.synchronize()
+            if s >= 2:
+                e2e_s += time.perf_counter() - t1; e2e_iters += e2e_lm.iterations()
+        n_lin, n_sol = max(phase["n_linearize"], 1.0), max(phase["n_solves"], 1.0)
+        return {"formulation": FORMULATION_NAMES["hybrid"], "value": iters / (dev_ms * 1e-3), "unit": "iter/s", "e2e": e2e_iters / e2e_s,
+                "factors": g.n_factors, "measurements": g.n_p2p, "poses": g.n_pose, "points": g.n_point, "final_chi2": chi2, "solve_residual": residual,
+                "linearize_ms": phase["linearize_ms"] / n_lin, "factor_linearisations_per_s": g.n_factors / (phase["linearize_ms"] / n_lin * 1e-3),
+                "linearize_hbm_frac": None, "schur_assemble_ms": phase["schur_assemble_ms"] / n_sol, "band_cholesky_ms": phase["band_cholesky_ms"] / n_sol,
+                "band_solve_ms": phase["band_solve_ms"] / n_sol, "lin_bytes": lin_bytes(g), "accuracy_final": acc}
+    finally:
+        FORMULATION = saved
+
+
 def run_ours(args, rank, world, local_rank):
     import numpy as np
     import torch
@@ -413,6 +452,10 @@ def run_ours(args, rank, world, local_rank):
         cpu_baseline = {"value": 1.0 / (per_iter * scale), "unit": "iter/s", "cores": cores, "kind": "port", "sample": cpu_sample_text(args.workload, sg, times, it, scale),
                         "phase_s_per_iteration": {k: v / max(it, 1) for k, v in phases.items()},
                         "what": "restated CPU oracle (oracle/): not GTSAM, which is unavailable on this box"}
+    hybrid = None
+    if world == 1 and FORMULATION == "world" and not args.no_hybrid and args.workload in ("cfg2", "cfg3"):
+        hybrid = measure_hybrid(args, local_rank)
+        hybrid["linearize_hbm_frac"] = hybrid["lin_bytes"] / (hybrid["linearize_ms"] * 1e-3) / 1e9 / hbm_peak
     verify = None
     if args.verify and world == 1:
         from oracle_lib import OracleGraph
@@ -439,7 +482,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches": launches,
         "roofline": roofline, "roofline_all": kernels, "cpu_baseline": cpu_baseline,
         "factor_linearisations_per_s": g.n_factors / (lin_ms * 1e-3),
-        "wall_ms_per_step": wall_ms / args.steps, "final_chi2": final_error, "solve_residual": residual, "verify": verify, "accuracy": accuracy,
+        "wall_ms_per_step": wall_ms / args.steps, "final_chi2": final_error, "solve_residual": residual, "verify": verify, "hybrid": hybrid, "accuracy": accuracy,
         "phase_ms_per_iteration": {k: phase[k] / max(iters if sharded_mode else iters / world, 1)
                                    for k in ("linearize_ms", "schur_assemble_ms", "band_cholesky_ms", "band_solve_ms", "evaluate_ms", "band_allreduce_ms")},
     }
@@ -583,6 +626,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS) + ["cfg4"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-hybrid", action="store_true", help="skip the extra measurement of the same workload in the hybrid formulation (N = 1)")
     ap.add_argument("--sharded", action="store_true", help="(default for N > 1) one scene partitioned over the GPUs by object and landmark: strong scaling")
     ap.add_argument("--replicas", action="store_true", help="N > 1: N independent replicas of the workload (weak scaling, no data-path collective) instead of the sharded solve")
     ap.add_argument("--verify", action="store_true", help="also run the CPU oracle with the same iteration budget on the same graph and print its chi^2 beside final_chi2")
