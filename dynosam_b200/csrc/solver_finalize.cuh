@@ -311,20 +311,21 @@ inline void LmSolver::finalize() {
   }
   // incidence records of the gather assembly, in list order: one 16-byte load instead of a chain of dependent index loads
   std::vector<int4> grec_p2p, grec_ter;
-  if (regular && theta_blocks < 0x7fffffffLL) {
-    grec_p2p.resize(pp_idx.size()); grec_ter.resize(pt_idx.size());
+  if (theta_blocks >= 0x7fffffffLL) regular = false;
+  grec_p2p.resize(pp_idx.size());
 #pragma omp parallel for schedule(static)
-    for (int64_t i = 0; i < (int64_t)pp_idx.size(); ++i) {
-      const int e = pp_idx[i], slot = p2p_slot[e], t = slot_step[slot];
-      grec_p2p[i] = make_int4(e, slot, t, t >= 0 ? (int)theta_off[slot] : 0);
-    }
+  for (int64_t i = 0; i < (int64_t)pp_idx.size(); ++i) {
+    const int e = pp_idx[i], slot = p2p_slot[e], t = slot_step[slot];
+    if (t >= 0) grec_p2p[i] = make_int4(e, slot, t, regular ? (int)theta_off[slot] : 0);   // tracklet point: (entry, slot, step, first Theta block)
+    else { const int rb = row_base[slot >> 5]; grec_p2p[i] = make_int4(e, slot, (e - rb) >> 5, rb); }   // chain of one: (entry, slot, place in its list, ELL row base)
+  }
+  if (regular) {
+    grec_ter.resize(pt_idx.size());
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < (int64_t)pt_idx.size(); ++i) {
       const int slot = pt_idx[i], t = slot_step[slot];
       grec_ter[i] = make_int4(-1, slot, t, (int)theta_off[slot] + t + 1);
     }
-  } else {
-    regular = false;
   }
   lap(3);
   build_csr(2 * n_btw, [&](int i) { return (i & 1) ? h_btw_b_[i >> 1] : h_btw_a_[i >> 1]; }, [&](int i) { return i; }, pb_ptr, pb_idx);
