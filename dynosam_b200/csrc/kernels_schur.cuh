@@ -553,7 +553,8 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_chain_gather(Device
                                                                           const int* __restrict__ p2p_slot, const double* __restrict__ Theta) {
   const int p = blockIdx.x;
   const int a = bs.pos_pose[p];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  // a row's batches are dealt to the warps of gridDim.y CTAs (a window of a few hundred poses would not fill the device otherwise)
+  const int lane = threadIdx.x & 31, wid = (threadIdx.x >> 5) + blockIdx.y * (blockDim.x >> 5), nw = (blockDim.x >> 5) * gridDim.y;
   const int sub = lane >> 3, sl = lane & 7;
   double acc[36], Ru[9];
   auto clear = [&]() {
@@ -636,7 +637,7 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_static_rows(DeviceG
   const int a = bs.pos_pose[p];
   const int ns = g.pose_p2p_nstatic[a];
   if (ns == 0) return;
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int lane = threadIdx.x & 31, wid = (threadIdx.x >> 5) + blockIdx.y * (blockDim.x >> 5), nw = (blockDim.x >> 5) * gridDim.y;
   const int sub = lane >> 3, sl = lane & 7;
   const int4* list = g.grec_p2p + g.pose_p2p_ptr[a];
   const int4 first = list[0];
