@@ -433,7 +433,7 @@ def run_ours(args, rank, world, local_rank):
     }
     # DRAM traffic per launch is a profiler figure (ncu --set full, profiles/README.md); it is copied in, never measured here
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             traffic = json.load(f).get(args.workload, {})
     except OSError:
         traffic = {}
