@@ -491,8 +491,11 @@ template <bool ROW_CAM>
 __device__ __forceinline__ void gather_accumulate(double (&acc)[36], const DeviceGraph& g, const int4* __restrict__ list, int n, int d, bool part_cam,
                                                   const double* __restrict__ Ru, const double4* __restrict__ p2p_qw, const double4* __restrict__ ter_qw,
                                                   const double* __restrict__ Theta, int sl) {
+  // the record of the next round is requested while this round's blocks are in flight: one memory round trip per round
+  int4 nxt = sl < n ? list[sl] : make_int4(0, 0, -1, 0);
   for (int i = sl; i < n; i += 8) {
-    const int4 rec = list[i];   // (entry, slot, step, first Theta block of this row)
+    const int4 rec = nxt;       // (entry, slot, step, first Theta block of this row)
+    if (i + 8 < n) nxt = list[i + 8];
     const int s = rec.y, t = rec.z;
     if (t < d + (part_cam ? 0 : 1)) break;   // sorted deepest first: nothing further reaches the partner
     const double* th = Theta + 9 * ((size_t)rec.w + d);
@@ -653,8 +656,10 @@ __global__ void __launch_bounds__(kGatherThreads, 2) k_schur_static_rows(DeviceG
     if (valid) {
       u = g.p2p_pose[first.w + (first.z - o) * 32 + (first.y & 31)];
       m3_load9(Ru, pose_lin + 12 * (size_t)u);
+      int4 nxt = sl < ns ? list[sl] : make_int4(0, 0, -1, 0);
       for (int i = sl; i < ns; i += 8) {
-        const int4 rec = list[i];
+        const int4 rec = nxt;
+        if (i + 8 < ns) nxt = list[i + 8];
         if (rec.z < o) break;
         const int ej = rec.w + (rec.z - o) * 32 + (rec.y & 31);
         const double4 ca = p2p_qw[rec.x];
