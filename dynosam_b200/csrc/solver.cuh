@@ -392,7 +392,7 @@ class LmSolver {
   DevBuf<int> d_seg_pose_, d_seg_lo_, d_pose_seg_ptr_, d_multi_pose_;   // segments of the pose-side gathers
   DevBuf<int> d_pose_nstatic_;
   DevBuf<int> d_slot_step_, d_cam_grp_ptr_, d_cam_grp_lo_, d_cam_grp_hi_;
-  DevBuf<long long> d_theta_off_;
+  DevBuf<long long> d_theta_off_, d_slice_theta_off_;
   DevBuf<int4> d_grec_p2p_, d_grec_ter_;
   DevBuf<double> d_Theta_;                    // Theta rows of the gather assembly (72 bytes a block)
   bool chains_regular_ = false, static_regular_ = false, use_gather_ = false;

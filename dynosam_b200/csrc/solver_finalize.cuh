@@ -115,8 +115,6 @@ inline void LmSolver::finalize() {
   // PoseToPoint factor from a camera key 'X' of frame F0 + t, every link (t-1, t) a motion key of one object label at frame
   // F0 + t: what the reference's formulation emits (Formulation-impl.hpp:308-584, WorldMotionEstimator.cc:155-238). Then
   // the chains of an object that pass through a pose and reach back d points all meet the same partner pose. ----
-  std::vector<int> slot_step(n_slots, -1);
-  std::vector<long long> theta_off(n_slots, 0);
   std::vector<int> first_p2p(npt, -1);
   {
     const int32_t* pts = in_p2p_point_.data();
@@ -134,7 +132,6 @@ inline void LmSolver::finalize() {
       int pt = chains[c].head;
       std::int64_t f0 = 0; unsigned char label = 0;
       for (int k = 0; k < chains[c].len; ++k) {
-        slot_step[slice_base[s] + k * 32 + lane] = k;
         if (degree[pt] != 1) { bad = true; }
         else {
           const Key ck = pose_keys_[in_p2p_pose_[first_p2p[pt]]];
@@ -156,16 +153,20 @@ inline void LmSolver::finalize() {
     }
     if (bad) regular = false;
   }
+  // Theta blocks: a tracklet of L points has L^2 + L - 1 of them (step t: t + 1 camera-row blocks, and as many motion-row
+  // blocks from t = 1 on); the per-slot offsets are filled in on the device from the per-slice ones (k_gather_tables)
   long long theta_blocks = 0;
+  std::vector<long long> slice_theta_off(n_slices + 1, 0);
   if (regular) {
-    for (int sl = 0; sl < n_slices; ++sl)
-      for (int k = 0; k < slice_len[sl]; ++k)
-        for (int lane = 0; lane < 32; ++lane) {
-          const int slot = slice_base[sl] + k * 32 + lane;
-          if (slot_step[slot] < 0) continue;
-          theta_off[slot] = theta_blocks;
-          theta_blocks += (k + 1) * (k >= 1 ? 2 : 1);
-        }
+#pragma omp parallel for schedule(static)
+    for (int sl = 0; sl < n_slices; ++sl) {
+      long long b = 0;
+      for (int lane = 0; lane < 32; ++lane) { const long long L = chain_len[(size_t)sl * 32 + lane]; if (L >= 2) b += L * L + L - 1; }
+      slice_theta_off[sl + 1] = b;
+    }
+    for (int sl = 0; sl < n_slices; ++sl) slice_theta_off[sl + 1] += slice_theta_off[sl];
+    theta_blocks = slice_theta_off[n_slices];
+    if (theta_blocks >= 0x7fffffffLL) regular = false;
   }
   lap(1);
   // ---- ELL rows of PoseToPoint factors ----
@@ -310,23 +311,6 @@ inline void LmSolver::finalize() {
     }
   }
   // incidence records of the gather assembly, in list order: one 16-byte load instead of a chain of dependent index loads
-  std::vector<int4> grec_p2p, grec_ter;
-  if (theta_blocks >= 0x7fffffffLL) regular = false;
-  grec_p2p.resize(pp_idx.size());
-#pragma omp parallel for schedule(static)
-  for (int64_t i = 0; i < (int64_t)pp_idx.size(); ++i) {
-    const int e = pp_idx[i], slot = p2p_slot[e], t = slot_step[slot];
-    if (t >= 0) grec_p2p[i] = make_int4(e, slot, t, regular ? (int)theta_off[slot] : 0);   // tracklet point: (entry, slot, step, first Theta block)
-    else { const int rb = row_base[slot >> 5]; grec_p2p[i] = make_int4(e, slot, (e - rb) >> 5, rb); }   // chain of one: (entry, slot, place in its list, ELL row base)
-  }
-  if (regular) {
-    grec_ter.resize(pt_idx.size());
-#pragma omp parallel for schedule(static)
-    for (int64_t i = 0; i < (int64_t)pt_idx.size(); ++i) {
-      const int slot = pt_idx[i], t = slot_step[slot];
-      grec_ter[i] = make_int4(-1, slot, t, (int)theta_off[slot] + t + 1);
-    }
-  }
   lap(3);
   build_csr(2 * n_btw, [&](int i) { return (i & 1) ? h_btw_b_[i >> 1] : h_btw_a_[i >> 1]; }, [&](int i) { return i; }, pb_ptr, pb_idx);
   build_csr(n_pri, [&](int i) { return h_pri_a_[i]; }, [&](int i) { return i; }, pr_ptr, pr_idx);
@@ -359,9 +343,23 @@ inline void LmSolver::finalize() {
   d_pose_pri_ptr_.upload(pr_ptr, stream_); d_pose_pri_idx_.upload(pr_idx, stream_);
   d_p2p_entry_of_input_.upload(p2p_entry_of_input_, stream_); d_ter_slot_of_input_.upload(ter_slot_of_input_, stream_);
   d_pose_nstatic_.upload(pose_nstatic, stream_);
-  d_slot_step_.upload(slot_step, stream_); d_theta_off_.upload(theta_off, stream_);
+  d_slice_theta_off_.upload(slice_theta_off, stream_);
+  d_slot_step_.alloc_raw(n_slots); d_theta_off_.alloc_raw(n_slots);
   d_cam_grp_ptr_.upload(cam_grp_ptr, stream_); d_cam_grp_lo_.upload(cam_grp_lo, stream_); d_cam_grp_hi_.upload(cam_grp_hi, stream_);
-  d_grec_p2p_.upload(grec_p2p, stream_); d_grec_ter_.upload(grec_ter, stream_);
+  // gather tables on the device (slot steps, Theta offsets, incidence records): pure functions of what was just uploaded
+  d_grec_p2p_.alloc_raw(pp_idx.size()); d_grec_ter_.alloc_raw(regular ? pt_idx.size() : 0);
+  if (n_slices) {
+    k_gather_tables<<<(n_slices * 32 + 127) / 128, 128, 0, stream_>>>(n_slices, d_slice_base_.p, d_slice_len_.p, d_chain_len_.p, d_slice_theta_off_.p, d_slot_step_.p, d_theta_off_.p);
+    launch_check("k_gather_tables");
+  }
+  {
+    const int n_pp = (int)pp_idx.size(), n_pt = (int)pt_idx.size(), n_max = std::max(n_pp, regular ? n_pt : 0);
+    if (n_max) {
+      k_gather_records<<<(n_max + 255) / 256, 256, 0, stream_>>>(n_pp, d_pose_p2p_idx_.p, n_pt, d_pose_ter_idx_.p, d_p2p_slot_.p, d_row_base_.p, d_slot_step_.p, d_theta_off_.p,
+                                                                d_grec_p2p_.p, regular ? d_grec_ter_.p : nullptr);
+      launch_check("k_gather_records");
+    }
+  }
   chains_regular_ = regular; theta_blocks_ = theta_blocks;
   d_seg_pose_.upload(seg_pose, stream_); d_seg_lo_.upload(seg_lo, stream_); d_pose_seg_ptr_.upload(pose_seg_ptr, stream_); d_multi_pose_.upload(multi_pose, stream_);
   // state
