@@ -11,6 +11,7 @@ from .api import (  # noqa: F401
     sliding_window_schedule,
 )
 from . import graphfile  # noqa: E402,F401  (DynoSAM text graph file reader / writer)
+from . import frontend_bson  # noqa: E402,F401  (the reference's recorded front-end packets, rgbd_frontend_output.bson)
 from . import metrics  # noqa: E402,F401  (ATE / RPE / object-motion error against scene ground truth)
 from . import postsolve  # noqa: E402,F401  (object pose propagation from the optimised motions, the reference logger CSV layout)
 from . import sharded  # noqa: E402,F401  (sharded solve over the GPUs of one box: partition, rank shares, NCCL exchange inside the library)
