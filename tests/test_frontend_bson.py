@@ -117,6 +117,8 @@ def test_reader_accepts_what_the_reference_adds_and_rejects_what_the_backend_can
     assert list(pk["motions"][0]) == [5, 6, 7] and list(pk["motions"][1]) == [2, 2, 2]
     scene = d.Scene.from_packets(pk["frame_id"], pk["T_world_camera"], pk["static"], pk["dynamic"], pk["motions"])
     assert scene.info() == {"n_frames": 3, "n_static_obs": 6, "n_dynamic_obs": 3}
+    with pytest.raises(RuntimeError):
+        scene.gt_camera()   # recorded packets carry no ground truth the library could hand back
     bad = {"data": [[0, dict(packet(0), static_landmarks=[dict(status(0, 1, 0, (0, 0, 1)), reference_frame="global")])]]}
     with pytest.raises(ValueError):
         fb.json_to_packets(bad)
