@@ -6,7 +6,7 @@ backend interface for that path. There is no CPU fallback.
 """
 from .api import (  # noqa: F401
     BackendParams, CameraPoseSymbol, DynamicLandmarkSymbol, DynoError, GpuLevenbergMarquardt, Graph, LmParams,
-    ObjectMotionSymbol, ObjectPoseSymbol, Scene, StaticLandmarkSymbol, SyntheticConfig, ValuesKeyDoesNotExist,
+    ObjectMotionSymbol, ObjectPoseSymbol, PipelinedLevenbergMarquardt, Scene, StaticLandmarkSymbol, SyntheticConfig, ValuesKeyDoesNotExist,
     cantor_depair, cantor_pair, default_backend_params, default_lm_params, default_synthetic_config, key_decode, measure_fp64_tflops,
     sliding_window_schedule,
 )
