@@ -49,7 +49,7 @@ struct DeviceGraph {
   const int* row_base = nullptr;     // [n_rows+1]
   const int* p2p_pose = nullptr;     // [entries] pose index or -1
   const unsigned char* p2p_group = nullptr;
-  const double* p2p_zx = nullptr; const double* p2p_zy = nullptr; const double* p2p_zz = nullptr;
+  const double4* p2p_z4 = nullptr;   // the measurement of an entry (x, y, z, 0): one 32-byte sector per factor for the pose-side gathers
   // ternary (slot indexed)
   const int* ter_motion = nullptr;   // [n_slots]
   const unsigned char* ter_group = nullptr;

@@ -20,7 +20,7 @@ __global__ void __launch_bounds__(256) k_export_p2p(DeviceGraph g, int64_t n, co
     for (int i = 0; i < 18; ++i) A_pose[18 * f + i] = s * J[i];
   }
   if (A_point) for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) A_point[9 * f + 3 * r + c] = s * pose_lin[12 * (size_t)a + 3 * c + r];  // R^T
-  if (b) { b[3 * f] = -s * (qw.x - g.p2p_zx[e]); b[3 * f + 1] = -s * (qw.y - g.p2p_zy[e]); b[3 * f + 2] = -s * (qw.z - g.p2p_zz[e]); }
+  if (b) { const double4 z = g.p2p_z4[e]; b[3 * f] = -s * (qw.x - z.x); b[3 * f + 1] = -s * (qw.y - z.y); b[3 * f + 2] = -s * (qw.z - z.z); }
 }
 
 __global__ void __launch_bounds__(256) k_export_ter(DeviceGraph g, int64_t n, const int* __restrict__ slot_of_input, const double* __restrict__ pose_lin,

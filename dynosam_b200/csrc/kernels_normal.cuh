@@ -57,7 +57,8 @@ __global__ void __launch_bounds__(256) k_build_poses(DeviceGraph g, const double
     const int e = g.pose_p2p_idx[k];
     const double4 c = p2p_qw[e];
     const V3 q = v3(c.x, c.y, c.z);
-    const V3 ev = v3(q.x - g.p2p_zx[e], q.y - g.p2p_zy[e], q.z - g.p2p_zz[e]);
+    const double4 zm = g.p2p_z4[e];
+    const V3 ev = v3(q.x - zm.x, q.y - zm.y, q.z - zm.z);
     acc_point_jtj(acc, c.w, q);
     // J^T b = -w [ e x q ; -e ]
     const V3 exq = cross3(ev, q);

@@ -268,7 +268,8 @@ __global__ void __launch_bounds__(256) k_lincost_points(DeviceGraph g, const dou
       const V3 q = v3(qw.x, qw.y, qw.z);
       V3 om, vv; load6(dx + 6 * (size_t)a, om, vv);
       M3 R; for (int i = 0; i < 9; ++i) R.a[i] = pose_lin[12 * (size_t)a + i];
-      const V3 ev = v3(q.x - g.p2p_zx[e], q.y - g.p2p_zy[e], q.z - g.p2p_zz[e]);
+      const double4 zm = g.p2p_z4[e];
+      const V3 ev = v3(q.x - zm.x, q.y - zm.y, q.z - zm.z);
       const V3 r = add(add(sub(cross3(q, om), vv), m3_apply_t(R, dp)), ev);
       acc += 0.5 * qw.w * dot3(r, r);
     }

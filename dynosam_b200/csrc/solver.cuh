@@ -388,7 +388,7 @@ class LmSolver {
   DevBuf<int> d_slice_base_, d_slice_len_, d_chain_len_, d_slot_point_, d_row_base_, d_p2p_pose_, d_p2p_slot_, d_ter_motion_;
   DevBuf<unsigned char> d_p2p_group_, d_ter_group_;
   DevBuf<NoiseGroup> d_noise_;
-  DevBuf<double> d_p2p_zx_, d_p2p_zy_, d_p2p_zz_;
+  DevBuf<double> d_p2p_z4_;
   DevBuf<int> d_btw_a_, d_btw_b_, d_pri_a_;
   DevBuf<double> d_btw_z_, d_btw_isig_, d_pri_z_, d_pri_isig_;
   DevBuf<int> d_pose_p2p_ptr_, d_pose_p2p_idx_, d_pose_ter_ptr_, d_pose_ter_idx_, d_pose_btw_ptr_, d_pose_btw_idx_, d_pose_pri_ptr_, d_pose_pri_idx_;
@@ -424,7 +424,7 @@ class LmSolver {
   DevBuf<long long> d_prof_;
   HostStage<int> hs_p2p_pose_, hs_p2p_slot_, hs_ter_motion_;
   HostStage<unsigned char> hs_p2p_group_, hs_ter_group_;
-  HostStage<double> hs_zx_, hs_zy_, hs_zz_, hs_pt4_;
+  HostStage<double> hs_z4_, hs_pt4_;
   bool band_ok_ = false, band_dirty_ = true, dpt_valid_ = false;
   int chol_grid_ = 0, back_grid_ = 0;
   int schur_split_ = 1;   // CTAs per pose in the Schur assembly

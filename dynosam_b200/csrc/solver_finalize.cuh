@@ -183,16 +183,14 @@ inline void LmSolver::finalize() {
   auto& p2p_pose = hs_p2p_pose_; p2p_pose.assign(n_entries, -1);
   auto& p2p_slot = hs_p2p_slot_; p2p_slot.assign(n_entries, -1);
   auto& p2p_group = hs_p2p_group_; p2p_group.assign(n_entries, 0);
-  auto& zx = hs_zx_; zx.assign(n_entries, 0.0);
-  auto& zy = hs_zy_; zy.assign(n_entries, 0.0);
-  auto& zz = hs_zz_; zz.assign(n_entries, 0.0);
+  auto& z4 = hs_z4_; z4.assign(4 * (size_t)n_entries, 0.0);   // (x, y, z, 0) per entry
   p2p_entry_of_input_.assign(n_p2p, -1);
 #pragma omp parallel for schedule(static)
   for (int64_t f = 0; f < n_p2p; ++f) {
     const int pt = in_p2p_point_[f], slot = point_slot_[pt];
     const int e = row_base[slot >> 5] + rank[f] * 32 + (slot & 31);
     p2p_pose[e] = in_p2p_pose_[f]; p2p_slot[e] = slot; p2p_group[e] = in_p2p_group_[f];
-    zx[e] = in_p2p_z_[3 * f]; zy[e] = in_p2p_z_[3 * f + 1]; zz[e] = in_p2p_z_[3 * f + 2];
+    z4[4 * (size_t)e] = in_p2p_z_[3 * f]; z4[4 * (size_t)e + 1] = in_p2p_z_[3 * f + 1]; z4[4 * (size_t)e + 2] = in_p2p_z_[3 * f + 2];
     p2p_entry_of_input_[f] = e;
   }
   lap(2);
@@ -333,7 +331,7 @@ inline void LmSolver::finalize() {
   d_slice_base_.upload(slice_base, stream_); d_slice_len_.upload(slice_len, stream_); d_chain_len_.upload(chain_len, stream_);
   d_slot_point_.upload(slot_point_, stream_); d_row_base_.upload(row_base, stream_);
   d_p2p_pose_.upload(p2p_pose, stream_); d_p2p_slot_.upload(p2p_slot, stream_); d_p2p_group_.upload(p2p_group, stream_);
-  d_p2p_zx_.upload(zx, stream_); d_p2p_zy_.upload(zy, stream_); d_p2p_zz_.upload(zz, stream_);
+  d_p2p_z4_.upload(z4, stream_);
   d_ter_motion_.upload(ter_motion, stream_); d_ter_group_.upload(ter_group, stream_);
   d_btw_a_.upload(h_btw_a_, stream_); d_btw_b_.upload(h_btw_b_, stream_); d_btw_z_.upload(h_btw_z_, stream_); d_btw_isig_.upload(h_btw_isig_, stream_);
   d_pri_a_.upload(h_pri_a_, stream_); d_pri_z_.upload(h_pri_z_, stream_); d_pri_isig_.upload(h_pri_isig_, stream_);
@@ -382,7 +380,7 @@ inline void LmSolver::finalize() {
   for (const DevBuf<int>* b : {&d_slice_base_, &d_slice_len_, &d_chain_len_, &d_slot_point_, &d_row_base_, &d_p2p_pose_, &d_p2p_slot_, &d_ter_motion_, &d_btw_a_, &d_btw_b_, &d_pri_a_,
                                &d_pose_p2p_ptr_, &d_pose_p2p_idx_, &d_pose_ter_ptr_, &d_pose_ter_idx_, &d_pose_btw_ptr_, &d_pose_btw_idx_, &d_pose_pri_ptr_, &d_pose_pri_idx_,
                                &d_p2p_entry_of_input_, &d_ter_slot_of_input_}) timing_[17] += (double)b->n * sizeof(int);
-  for (const DevBuf<double>* b : {&d_p2p_zx_, &d_p2p_zy_, &d_p2p_zz_, &d_btw_z_, &d_btw_isig_, &d_pri_z_, &d_pri_isig_, &d_pose_a_, &d_pt_a_}) timing_[17] += (double)b->n * sizeof(double);
+  for (const DevBuf<double>* b : {&d_p2p_z4_, &d_btw_z_, &d_btw_isig_, &d_pri_z_, &d_pri_isig_, &d_pose_a_, &d_pt_a_}) timing_[17] += (double)b->n * sizeof(double);
   timing_[17] += (double)d_p2p_group_.n + (double)d_ter_group_.n + (double)kMaxNoiseGroups * sizeof(NoiseGroup);
 
   d_p2p_qw_.alloc(n_entries); d_ter_qw_.alloc(n_slots);
@@ -403,7 +401,7 @@ inline void LmSolver::finalize() {
   g_.noise = d_noise_.p;
   g_.slice_base = d_slice_base_.p; g_.slice_len = d_slice_len_.p; g_.chain_len = d_chain_len_.p; g_.slot_point = d_slot_point_.p;
   g_.row_base = d_row_base_.p; g_.p2p_pose = d_p2p_pose_.p; g_.p2p_group = d_p2p_group_.p;
-  g_.p2p_zx = d_p2p_zx_.p; g_.p2p_zy = d_p2p_zy_.p; g_.p2p_zz = d_p2p_zz_.p;
+  g_.p2p_z4 = reinterpret_cast<const double4*>(d_p2p_z4_.p);
   g_.ter_motion = d_ter_motion_.p; g_.ter_group = d_ter_group_.p;
   g_.btw_a = d_btw_a_.p; g_.btw_b = d_btw_b_.p; g_.btw_z = d_btw_z_.p; g_.btw_isig = d_btw_isig_.p;
   g_.pri_a = d_pri_a_.p; g_.pri_z = d_pri_z_.p; g_.pri_isig = d_pri_isig_.p;
