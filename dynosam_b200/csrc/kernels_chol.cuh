@@ -43,7 +43,8 @@ __device__ __forceinline__ double fast_rsqrt(double d) {
 }
 
 // 1/d to double precision: hardware f64 seed y0 (relative error e0 ~ 2^-20 or better), then the cubic step
-// y = y0 (1 + e + e^2), e = 1 - d y0, which leaves e0^3. Three dependent FP64 operations (about 55 cycles each here)
+// y = y0 (1 + e + e^2), e = 1 - d y0, which leaves e0^3. Three dependent FP64 operations (8.4 cycles of latency each when nothing else is
+// in the way, tools/fp64_latency_probe.cu; a single warp also issues at most one warp-wide DFMA per 2.1 cycles)
 // instead of the four of two Newton steps: this is the only non-FMA work on the chain of the diagonal factorisation.
 __device__ __forceinline__ double fast_rcp(double d) {
   double y0;
@@ -358,8 +359,8 @@ __device__ __forceinline__ void band_diag_inverse_block(const BandSystem& bs, in
 // element k (k = lane, lane + 32) of a 64-vector held as v0/v1 across a warp:  v <- v L^-T  (rows: x L^T = a).
 // Ds = L with column m scaled by rd[m] = 1 / L_mm (64 x 64 lower, row stride 65, shared memory). With u_m the running
 // residual entry, x_m = u_m rd[m] and every later entry loses u_m Ds[j][m]: the serial chain per column is one shuffle
-// and one FMA (a dependent FP64 operation costs about 55 cycles on this part, so the multiply by rd[m] is kept off the
-// chain, and written as straight-line selects: a divergent branch around it serialises the two sides).
+// and one FMA (a step of that chain measured about 70 ns here: shuffle latency plus the pipe's issue rate for a single
+// warp, not the 8-cycle FMA latency; the multiply by rd[m] is kept off the chain, and written as straight-line selects: a divergent branch around it serialises the two sides).
 __device__ __forceinline__ void warp_trsm64(double& v0, double& v1, const double* __restrict__ Ds, const double* __restrict__ rd, int lane) {
 #pragma unroll 8
   for (int m = 0; m < 32; ++m) {
