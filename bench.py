@@ -400,7 +400,7 @@ def run_ours(args, rank, world, local_rank):
     # warm-up step to the completion of the last timed step, with one more graph queued behind it so that the last timed
     # solve has a hand-over beside it like every other.
     pipe_s, pipe_iters = 0.0, 0
-    if not sharded_mode:
+    if world == 1:                   # (N replicas on one host would put N flattening teams on the same cores: measured slower than one step at a time)
         pipe = d.PipelinedLevenbergMarquardt(p)
         n_warm, stamps, its = 2, [], []
         barrier()
@@ -432,7 +432,7 @@ def run_ours(args, rank, world, local_rank):
                "one_step_at_a_time": serial}
     else:
         e2e = {"value": serial["value"], "unit": "iter/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": serial["ms_per_step"],
-               "mode": "one step at a time (the sharded solve has one handle per rank)"}
+               "mode": "one step at a time"}
     n_lin, n_sol = max(phase["n_linearize"], 1.0), max(phase["n_solves"], 1.0)
     lin_ms, sch_ms, cho_ms = phase["linearize_ms"] / n_lin, phase["schur_assemble_ms"] / n_sol, phase["band_cholesky_ms"] / n_sol
     peaks = {}
